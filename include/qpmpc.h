@@ -1,0 +1,171 @@
+/*
+ * qpmpc.h -- C ABI of libqpmpc_b200.so: the B200-native (sm_100a, hand-written CUDA) replacement for the
+ * sampling-based centroidal MPC hot path of iit-DLSLab/Quadruped-PyMPC.
+ *
+ * Reference surface replaced (paths relative to the reference's quadruped_pympc/):
+ *   S = controllers/sampling/centroidal_nmpc_jax.py            (Sampling_MPC, fixed gait)
+ *   A = controllers/sampling/centroidal_nmpc_jax_gait_adaptive.py (Sampling_MPC, gait adaptive)
+ *   M = controllers/sampling/centroidal_model_jax.py           (Centroidal_Model_JAX)
+ *   G = helpers/periodic_gait_generator_jax.py                 (PeriodicGaitGeneratorJax)
+ *   I = interfaces/srbd_controller_interface.py                (the caller; unchanged)
+ *
+ * Plain C: pointers + sizes, no torch / C++ types.  All functions return QPMPC_OK (0) or a negative
+ * qpmpc_status; qpmpc_last_error() gives the message of the last failure on the calling thread.
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with QPMPC_ERR_CUDA.
+ * A handle is not thread-safe (one tick in flight per controller, like the reference, I:118-168) and must be
+ * created in the process that ticks it (CUDA contexts do not survive fork(); ros2/run_controller.py:225-243).
+ */
+#ifndef QPMPC_H
+#define QPMPC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QPMPC_ABI_VERSION 1
+#define QPMPC_MAX_HORIZON 64
+#define QPMPC_MAX_SPLINES 16
+#define QPMPC_MAX_ELITE 256
+#define QPMPC_STATE_DIM 24  /* S:35 */
+
+typedef enum {
+    QPMPC_OK = 0,
+    QPMPC_ERR_INVALID = -1,   /* bad argument / configuration (reference: sys.exit(1) on unknown method, S:107-110) */
+    QPMPC_ERR_CUDA = -2,      /* CUDA runtime failure or no device: the product path has no CPU fallback */
+    QPMPC_ERR_NCCL = -3,      /* NCCL unavailable or failed (sample-sharded controllers only) */
+    QPMPC_ERR_STATE = -4      /* call sequence error (e.g. finish without partial) */
+} qpmpc_status;
+
+/* mpc_params['control_parametrization'], config.py:185; S:52-93 */
+typedef enum { QPMPC_ZERO_ORDER = 0, QPMPC_LINEAR_SPLINE = 1, QPMPC_CUBIC_SPLINE = 2 } qpmpc_parametrization;
+/* mpc_params['sampling_method'], config.py:184; S:96-110 */
+typedef enum { QPMPC_RANDOM_SAMPLING = 0, QPMPC_MPPI = 1, QPMPC_CEM_MPPI = 2 } qpmpc_method;
+
+/* Host<->device transport of the per-tick packet (inputs ~1 KB, outputs ~1 KB). */
+typedef enum {
+    QPMPC_IO_MEMCPY = 0,  /* pinned staging + cudaMemcpyAsync H2D / D2H around the kernel */
+    QPMPC_IO_MAPPED = 1   /* kernel reads/writes mapped pinned host memory directly (zero-copy over PCIe) */
+} qpmpc_io_mode;
+
+/* Everything Sampling_MPC.__init__ (S:23-177 / A:24-187) and Centroidal_Model_JAX.__init__ (M:20-65) freeze. */
+typedef struct qpmpc_config {
+    int32_t abi_version;          /* = QPMPC_ABI_VERSION */
+    int32_t num_samples;          /* N = mpc_params['num_parallel_computations'], config.py:187 */
+    int32_t horizon;              /* H, config.py:92 (<= QPMPC_MAX_HORIZON) */
+    int32_t num_splines;          /* config.py:186 */
+    int32_t parametrization;      /* qpmpc_parametrization */
+    int32_t method;               /* qpmpc_method */
+    int32_t adaptive;             /* mpc_params['optimize_step_freq'], config.py:108 -> A instead of S (I:77-83) */
+    int32_t num_robots;           /* R >= 1: independent controllers batched in one launch (simulation/batched_simulations.py) */
+    int32_t device;               /* CUDA device ordinal */
+    int32_t io_mode;              /* qpmpc_io_mode */
+    int32_t use_graph;            /* 1: capture (H2D, kernel, D2H) in a CUDA graph and replay it per tick */
+    int32_t shard_rank;           /* sample-split controller: this handle owns a slice of the N samples */
+    int32_t shard_world;          /* 1 = not sharded */
+    int32_t elite_k;              /* 0 = reference default (10 fixed gait S:1075, 200 adaptive A:1115) */
+    uint32_t seed;                /* Philox key word 0 (the reference seeds PRNGKey(42), S:167) */
+    float mass;                   /* config.mass, M:38 */
+    float inertia[9];             /* config.inertia row-major, M:39 */
+    float dts[QPMPC_MAX_HORIZON]; /* M:42-53 (uniform dt or fine-grained head) */
+    float mu;                     /* S:160 */
+    float grf_min, grf_max;       /* S:163-164 */
+    float q_diag[12];             /* S:118-130 (entries 12..23 of Q are zero) */
+    float sigma_random_sampling[3]; /* config.py:193 */
+    float sigma_mppi;             /* config.py:192 */
+    float step_freq_available[3]; /* config.py:109 */
+    float pgg_duty_factor;        /* 0.65 hard-coded in A:179 */
+} qpmpc_config;
+
+/* One robot's inputs for one tick = the arguments of jitted_compute_control (I:140-168) */
+typedef struct qpmpc_tick_in {
+    const float *state;            /* 24: [pos, lin vel, rpy, ang vel (base), foot FL, FR, RL, RR], S:575-586 */
+    const float *reference;        /* 24, same order, S:597-608 */
+    const float *contact_sequence; /* 4 rows (FL,FR,RL,RR) x >=H columns, values exactly 0 or 1 */
+    int32_t contact_ld;            /* row stride of contact_sequence in floats (caller may pass a (4,2H) table) */
+    const float *best;             /* P: best_control_parameters going in (S:634) */
+    const float *sigma;            /* P: cem_mppi sigma (S:941); NULL otherwise */
+    const float *phase_signal;     /* 4: pgg_phase_signal ("timing", A:326); may be NULL when not adaptive */
+    float nominal_step_freq;       /* A:637 */
+    int32_t optimize_swing;        /* A:638 */
+    uint32_t key[2];               /* (seed, counter): the controller's master_key (S:498-501) */
+    /* parity hooks (north_star: "with the reference's noise tensor injected"); NULL in production */
+    const float *noise;            /* N x P additional_random_parameters (S:647-677), row-major, host memory */
+    const float *step_freqs;       /* N per-sample step frequencies (A:688-692), host memory */
+} qpmpc_tick_in;
+
+/* One robot's outputs = the tuple jitted_compute_control returns (S:786-787, S:1085-1094, A:798-806) */
+typedef struct qpmpc_tick_out {
+    float grfs[12];               /* nmpc_GRFs [FL xyz, FR, RL, RR], S:747 */
+    float predicted_state[24];    /* nmpc_predicted_state, S:784 */
+    float best_cost;              /* S:691 */
+    float best_freq;              /* 1.4 / 1.65 constants (S:786,1083) or the best sample's frequency (A:705) */
+    int32_t best_index;           /* nanargmin(costs), S:690 (global sample index) */
+    int32_t num_elite;            /* cem_mppi: number of elite indices written */
+    float *best;                  /* P, caller-allocated: best_control_parameters coming out */
+    float *sigma_new;             /* P, caller-allocated or NULL: new_sigma_cem_mppi, S:1077-1081 */
+    int32_t *elite_indices;       /* elite_k, caller-allocated or NULL: argsort(costs)[:k], S:1075 */
+} qpmpc_tick_out;
+
+typedef struct qpmpc_handle qpmpc_handle;
+
+/* ---- lifecycle -------------------------------------------------------------------------------------- */
+int qpmpc_abi_version(void);
+const char *qpmpc_last_error(void);
+int qpmpc_device_count(int *count);                       /* QPMPC_ERR_CUDA when no driver / device */
+void qpmpc_config_defaults(qpmpc_config *cfg);            /* config.py defaults for robot 'go2' */
+int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out);   /* replaces Sampling_MPC.__init__, S:23-177 */
+void qpmpc_destroy(qpmpc_handle *h);
+int qpmpc_num_parameters(const qpmpc_handle *h);          /* P = num_control_parameters, S:52-93 */
+int qpmpc_num_local_samples(const qpmpc_handle *h);       /* samples evaluated by this shard */
+
+/* ---- the tick: replaces Sampling_MPC.jitted_compute_control (S:112, called at I:140/159) ------------- */
+int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
+/* R robots in one launch (replaces "one process per robot", simulation/batched_simulations.py:43-58).
+ * in / out are arrays of num_robots structs; parity hooks noise/step_freqs are honoured per robot. */
+int qpmpc_tick_batched(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
+/* costs (N) of the last tick of robot r, fetched lazily (the interface ignores them, I:138,158) */
+int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst);
+
+/* ---- the RNG-free seam: replaces jit_vectorized_rollout (S:176-177 / A:186-187) ----------------------- */
+/* params: N x P explicit control parameters (host); step_freqs: N or NULL; costs: N (raw, not saturated) */
+int qpmpc_rollout(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                  int32_t contact_ld, const float *phase_signal, const float *params, const float *step_freqs,
+                  float *costs);
+
+/* ---- noise generator export (debug / parity): the (rows x P) additional_random_parameters the tick with
+ * key (seed,counter) would draw for robot r; sigma (P) only for cem_mppi.  Same device code as the tick. */
+int qpmpc_generate_noise(qpmpc_handle *h, int robot, const uint32_t key[2], const float *sigma, float *dst);
+/* per-sample step frequencies (N) the adaptive tick would draw (A:688-692 | A:835-838 | A:994-1000) */
+int qpmpc_generate_step_freqs(qpmpc_handle *h, int robot, const uint32_t key[2], float nominal_step_freq,
+                              int32_t optimize_swing, float *dst);
+
+/* ---- sample-sharded controller, one shard per GPU.  partial = rollouts + local reduction into a
+ * device-resident record; finish = merge `world` records (gathered by NCCL or by the caller) + tail. -------- */
+int qpmpc_shard_record_floats(const qpmpc_handle *h);     /* floats per shard record */
+int qpmpc_shard_partial(qpmpc_handle *h, const qpmpc_tick_in *in);           /* async on the handle's stream */
+int qpmpc_shard_record_device_ptr(qpmpc_handle *h, void **send, void **recv); /* device buffers: 1 / world records */
+int qpmpc_shard_finish(qpmpc_handle *h, qpmpc_tick_out *out);                /* merges recv[0..world) */
+int qpmpc_shard_copy_record(qpmpc_handle *h, int slot, const float *host_rec); /* tests: fill recv[slot] from host */
+int qpmpc_shard_get_record(qpmpc_handle *h, float *host_rec);                /* tests: read send record */
+/* NCCL plumbing (dlopen of libnccl.so.2; no link-time dependency).  id: 128-byte ncclUniqueId. */
+int qpmpc_nccl_unique_id(const char *libnccl_path, unsigned char id[128]);
+int qpmpc_shard_init_nccl(qpmpc_handle *h, const char *libnccl_path, const unsigned char id[128]);
+int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out); /* partial+allgather+finish */
+
+/* ---- device-resident benchmarking helpers (inputs already in HBM; CUDA-event timing on the handle's stream) */
+/* Upload one packet per robot and keep it resident; subsequent qpmpc_bench_resident calls replay it. */
+int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in);
+/* Runs `steps` resident ticks; ms[i] = device time of tick i (events around the kernel(s) only).  If
+ * flush_l2 != 0 a buffer larger than L2 is rewritten before every timed tick (outside the events). */
+int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms);
+int qpmpc_fetch_resident_out(qpmpc_handle *h, qpmpc_tick_out *out);  /* D2H of the last resident tick's outputs */
+int qpmpc_kernel_launch_count(const qpmpc_handle *h, uint64_t *count); /* kernels launched by this handle so far */
+/* FP32 FMA peak of the device (dependent-free FFMA streams on every SM), TFLOP/s; sm_mhz may be NULL */
+int qpmpc_measure_fp32_peak(int device, float *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QPMPC_H */

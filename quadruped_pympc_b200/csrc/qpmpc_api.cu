@@ -1,0 +1,784 @@
+// qpmpc_api.cu -- host side of libqpmpc_b200.so: the C ABI declared in include/qpmpc.h.
+// No CPU fallback anywhere: every compute entry point needs a CUDA device and fails with QPMPC_ERR_CUDA otherwise.
+#include "../../include/qpmpc.h"
+#include "qpmpc_tick.cuh"
+
+#include <dlfcn.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace qp;
+
+// ------------------------------------------------------------------------------------------------------
+// error plumbing
+// ------------------------------------------------------------------------------------------------------
+static thread_local std::string g_err = "";
+static int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CK(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess) return fail(QPMPC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------------
+// small kernels: finish stage of a sharded tick, noise / frequency export, FP32 peak probe
+// ------------------------------------------------------------------------------------------------------
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__global__ void __launch_bounds__(TB, 4) finish_kernel(const __grid_constant__ KParams kp) {
+    extern __shared__ __align__(16) float smem_raw[];
+    const Smem s(smem_raw, kp);
+    const int r = blockIdx.y;
+    stage_inputs(kp, r, s);
+    finish<PARAM, ADAPTIVE, METHOD>(kp, r, s, kp.shard_recv + (size_t)r * kp.shard_rec_stride, kp.world,
+                                    (size_t)gridDim.y * kp.shard_rec_stride);
+}
+
+template <int METHOD>
+__global__ void noise_export_kernel(const __grid_constant__ KParams kp, uint32_t seed, uint32_t robot, uint32_t tick,
+                                    const float *sigma, float *dst) {
+    const int nq = kp.P / 4;
+    const size_t total = (size_t)kp.N * nq;
+    for (size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(w / nq), q = (int)(w - (size_t)i * nq);
+        const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, i, q, sigma);
+        reinterpret_cast<float4 *>(dst)[w] = e;      // (N,P) row-major, float4-vectorised and coalesced
+    }
+}
+
+template <int METHOD>
+__global__ void freq_export_kernel(const __grid_constant__ KParams kp, const float *in_rec, float *dst) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kp.N; i += gridDim.x * blockDim.x)
+        dst[i] = sample_step_freq<METHOD>(kp, in_rec, 0, i);
+}
+
+__global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
+    float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+// ------------------------------------------------------------------------------------------------------
+// kernel dispatch tables (parametrisation x adaptive x method)
+// ------------------------------------------------------------------------------------------------------
+typedef void (*KernelFn)(const KParams);
+#define QP_ROW(K, P, A) {K<P, A, RANDOM_SAMPLING>, K<P, A, MPPI>, K<P, A, CEM_MPPI>}
+#define QP_TABLE(K) {{QP_ROW(K, ZERO_ORDER, false), QP_ROW(K, ZERO_ORDER, true)},   \
+                     {QP_ROW(K, LINEAR, false), QP_ROW(K, LINEAR, true)},           \
+                     {QP_ROW(K, CUBIC, false), QP_ROW(K, CUBIC, true)}}
+static KernelFn g_tick_table[3][2][3] = QP_TABLE(tick_kernel);
+static KernelFn g_finish_table[3][2][3] = QP_TABLE(finish_kernel);
+
+// ------------------------------------------------------------------------------------------------------
+// NCCL through dlopen (no link-time dependency; the torch-bundled libnccl.so.2 is passed in by the host code)
+// ------------------------------------------------------------------------------------------------------
+struct NcclId { char internal[128]; };
+typedef void *NcclComm;
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(NcclId *) = nullptr;
+    int (*CommInitRank)(NcclComm *, int, NcclId, int) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, NcclComm, cudaStream_t) = nullptr;
+    int (*CommDestroy)(NcclComm) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+static int load_nccl(const char *path) {
+    if (g_nccl.lib) return QPMPC_OK;
+    void *lib = dlopen(path && path[0] ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail(QPMPC_ERR_NCCL, "dlopen(%s) failed: %s", path ? path : "libnccl.so.2", dlerror());
+    g_nccl.GetUniqueId = (int (*)(NcclId *))dlsym(lib, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (int (*)(NcclComm *, int, NcclId, int))dlsym(lib, "ncclCommInitRank");
+    g_nccl.AllGather = (int (*)(const void *, void *, size_t, int, NcclComm, cudaStream_t))dlsym(lib, "ncclAllGather");
+    g_nccl.CommDestroy = (int (*)(NcclComm))dlsym(lib, "ncclCommDestroy");
+    g_nccl.GetErrorString = (const char *(*)(int))dlsym(lib, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.CommDestroy)
+        return fail(QPMPC_ERR_NCCL, "libnccl is missing required symbols");
+    g_nccl.lib = lib;
+    return QPMPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// the handle
+// ------------------------------------------------------------------------------------------------------
+struct qpmpc_handle {
+    qpmpc_config cfg;
+    KParams kp;                       // template: constants + device pointers for MODE_TICK
+    int R, N, H, P, n_local;
+    size_t smem_bytes;
+    cudaStream_t stream = nullptr;
+    float *d_in = nullptr, *d_out = nullptr, *d_costs = nullptr, *d_blk = nullptr, *d_send = nullptr, *d_recv = nullptr;
+    float *d_noise = nullptr, *d_freqs = nullptr, *d_flush = nullptr, *d_sigma = nullptr;
+    unsigned int *d_counters = nullptr;
+    float *h_in = nullptr, *h_out = nullptr, *h_rec = nullptr;   // pinned (mapped when io_mode == MAPPED)
+    float *kin = nullptr, *kout = nullptr;                       // what the kernel dereferences for in / out
+    size_t noise_capacity = 0, freqs_capacity = 0;
+    cudaGraphExec_t graph_exec = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint64_t launches = 0;
+    bool resident_uploaded = false, partial_done = false;
+    NcclComm comm = nullptr;
+    KernelFn tick_fn = nullptr, finish_fn = nullptr;
+};
+
+static size_t round4(size_t x) { return (x + 3) & ~(size_t)3; }
+
+static int chunk_index_host(const qpmpc_config *c, float stepf, const float *bounds) {
+    int idx = 0;
+    for (int i = 0; i <= c->num_splines; ++i)
+        if (stepf >= bounds[i] && i > idx) idx = i;
+    return idx;
+}
+
+// 3x3 inverse by cofactors in float32, same expression as M:67-91
+static void inv3f(const float A[9], float out[9]) {
+    const float a11 = A[0], a12 = A[1], a13 = A[2], a21 = A[3], a22 = A[4], a23 = A[5], a31 = A[6], a32 = A[7], a33 = A[8];
+    const float DET = a11 * (a33 * a22 - a32 * a23) - a21 * (a33 * a12 - a32 * a13) + a31 * (a23 * a12 - a22 * a13);
+    out[0] = (a33 * a22 - a32 * a23) / DET;  out[1] = -(a33 * a12 - a32 * a13) / DET; out[2] = (a23 * a12 - a22 * a13) / DET;
+    out[3] = -(a33 * a21 - a31 * a23) / DET; out[4] = (a33 * a11 - a31 * a13) / DET;  out[5] = -(a23 * a11 - a21 * a13) / DET;
+    out[6] = (a32 * a21 - a31 * a22) / DET;  out[7] = -(a32 * a11 - a31 * a12) / DET; out[8] = (a22 * a11 - a21 * a12) / DET;
+}
+
+static int validate_config(const qpmpc_config *c) {
+    if (!c) return fail(QPMPC_ERR_INVALID, "config is NULL");
+    if (c->abi_version != QPMPC_ABI_VERSION) return fail(QPMPC_ERR_INVALID, "abi_version %d != %d", c->abi_version, QPMPC_ABI_VERSION);
+    if (c->num_samples < 1) return fail(QPMPC_ERR_INVALID, "num_samples must be >= 1");
+    if (c->horizon < 1 || c->horizon > QPMPC_MAX_HORIZON) return fail(QPMPC_ERR_INVALID, "horizon must be in [1,%d]", QPMPC_MAX_HORIZON);
+    if (c->parametrization < 0 || c->parametrization > 2) return fail(QPMPC_ERR_INVALID, "unknown control parametrization %d", c->parametrization);
+    if (c->method < 0 || c->method > 2) return fail(QPMPC_ERR_INVALID, "Error: sampling method not recognized (%d)", c->method);  // S:107-110
+    if (c->parametrization != QPMPC_ZERO_ORDER && (c->num_splines < 1 || c->num_splines > QPMPC_MAX_SPLINES))
+        return fail(QPMPC_ERR_INVALID, "num_splines must be in [1,%d]", QPMPC_MAX_SPLINES);
+    if (c->num_robots < 1) return fail(QPMPC_ERR_INVALID, "num_robots must be >= 1");
+    if (c->shard_world < 1 || c->shard_rank < 0 || c->shard_rank >= c->shard_world) return fail(QPMPC_ERR_INVALID, "bad shard rank/world");
+    if (!(c->mass > 0.f)) return fail(QPMPC_ERR_INVALID, "mass must be positive");
+    if (c->elite_k < 0 || c->elite_k > QPMPC_MAX_ELITE) return fail(QPMPC_ERR_INVALID, "elite_k must be in [0,%d]", QPMPC_MAX_ELITE);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_abi_version(void) { return QPMPC_ABI_VERSION; }
+extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
+
+extern "C" int qpmpc_device_count(int *count) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { if (count) *count = 0; return fail(QPMPC_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e)); }
+    if (count) *count = n;
+    return QPMPC_OK;
+}
+
+extern "C" void qpmpc_config_defaults(qpmpc_config *c) {
+    memset(c, 0, sizeof(*c));
+    c->abi_version = QPMPC_ABI_VERSION;
+    c->num_samples = 10000; c->horizon = 12; c->num_splines = 2;                 // config.py:92,186,187
+    c->parametrization = QPMPC_CUBIC_SPLINE; c->method = QPMPC_RANDOM_SAMPLING;  // config.py:184-185
+    c->adaptive = 0; c->num_robots = 1; c->device = 0; c->io_mode = QPMPC_IO_MEMCPY; c->use_graph = 1;
+    c->shard_rank = 0; c->shard_world = 1; c->elite_k = 0; c->seed = 42u;        // S:167
+    c->mass = 15.019f;                                                            // go2, config.py:25-29
+    const float I[9] = {1.58460467e-01f, 1.21660000e-04f, -1.55444692e-02f, 1.21660000e-04f, 4.68645637e-01f,
+                        -3.12000000e-05f, -1.55444692e-02f, -3.12000000e-05f, 5.24474661e-01f};
+    memcpy(c->inertia, I, sizeof(I));
+    for (int i = 0; i < QPMPC_MAX_HORIZON; ++i) c->dts[i] = 0.02f;               // config.py:93
+    c->mu = 0.5f; c->grf_min = 0.f; c->grf_max = (float)(15.019 * 9.81);         // config.py:96-98
+    const float q[12] = {0, 0, 1500, 200, 200, 200, 500, 500, 0, 20, 20, 50};    // S:118-130
+    memcpy(c->q_diag, q, sizeof(q));
+    c->sigma_random_sampling[0] = 0.2f; c->sigma_random_sampling[1] = 3.f; c->sigma_random_sampling[2] = 10.f;
+    c->sigma_mppi = 3.f;
+    c->step_freq_available[0] = 1.4f; c->step_freq_available[1] = 2.0f; c->step_freq_available[2] = 2.4f;
+    c->pgg_duty_factor = 0.65f;                                                   // A:179
+}
+
+static void free_handle(qpmpc_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    cudaFree(h->d_in); cudaFree(h->d_out); cudaFree(h->d_costs); cudaFree(h->d_blk); cudaFree(h->d_send); cudaFree(h->d_recv);
+    cudaFree(h->d_noise); cudaFree(h->d_freqs); cudaFree(h->d_flush); cudaFree(h->d_counters); cudaFree(h->d_sigma);
+    if (h->h_in) cudaFreeHost(h->h_in);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->h_rec) cudaFreeHost(h->h_rec);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+extern "C" void qpmpc_destroy(qpmpc_handle *h) { free_handle(h); }
+
+static void plan_blocks(int n_local, int *iters, int *nblk) {
+    const int tiles = (n_local + TB - 1) / TB;
+    const int cap = 148 * 4 * 2;                       // two full waves of resident CTAs on 148 SMs
+    int it = (tiles + cap - 1) / cap;
+    if (it < 1) it = 1;
+    *iters = it;
+    *nblk = (tiles + it - 1) / it;
+}
+
+extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
+    if (!out) return fail(QPMPC_ERR_INVALID, "out handle pointer is NULL");
+    *out = nullptr;
+    int rc = validate_config(cfg);
+    if (rc) return rc;
+    int ndev = 0;
+    rc = qpmpc_device_count(&ndev);
+    if (rc) return rc;
+    if (ndev == 0) return fail(QPMPC_ERR_CUDA, "no CUDA device: libqpmpc_b200 has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(QPMPC_ERR_INVALID, "device %d out of range (%d devices)", cfg->device, ndev);
+    CK(cudaSetDevice(cfg->device));
+
+    qpmpc_handle *h = new qpmpc_handle();
+    h->cfg = *cfg;
+    const int H = cfg->horizon, ns = cfg->parametrization == QPMPC_ZERO_ORDER ? 1 : cfg->num_splines;
+    h->H = H; h->N = cfg->num_samples; h->R = cfg->num_robots;
+    int P_leg;
+    if (cfg->parametrization == QPMPC_LINEAR_SPLINE) P_leg = (ns + 1) * 3;          // S:56
+    else if (cfg->parametrization == QPMPC_CUBIC_SPLINE) P_leg = 4 * 3 * ns;        // S:71
+    else P_leg = H * 3;                                                              // S:84
+    h->P = 4 * P_leg;
+    if (h->P > MAXV * TB) { delete h; return fail(QPMPC_ERR_INVALID, "P = %d control parameters exceed the kernel limit %d", 4 * P_leg, MAXV * TB); }
+    // contiguous sample slice of this shard (global index = base + local keeps argmin / elite indices global)
+    const int W = cfg->shard_world, rk = cfg->shard_rank;
+    const int per = (h->N + W - 1) / W;
+    const int base = std::min(per * rk, h->N);
+    h->n_local = std::min(per, h->N - base);
+    if (h->n_local < 1) { delete h; return fail(QPMPC_ERR_INVALID, "shard %d of %d owns no samples (N=%d)", rk, W, h->N); }
+    int elite_k = cfg->elite_k > 0 ? cfg->elite_k : (cfg->adaptive ? 200 : 10);     // A:1115 | S:1075
+    if (cfg->method != QPMPC_CEM_MPPI) elite_k = 0;
+    if (W * elite_k > SCRATCH_KEYS) { delete h; return fail(QPMPC_ERR_INVALID, "shard_world * elite_k = %d exceeds %d", W * elite_k, SCRATCH_KEYS); }
+
+    KParams &kp = h->kp;
+    memset(&kp, 0, sizeof(kp));
+    kp.N = h->N; kp.n_local = h->n_local; kp.sample_base = base;
+    kp.H = H; kp.ns = ns; kp.P = h->P; kp.P_leg = P_leg;
+    plan_blocks(h->n_local, &kp.iters, &kp.nblk);
+    kp.elite_k = elite_k;
+    kp.mode = MODE_TICK; kp.noise_mode = NOISE_PHILOX; kp.freq_injected = 0;
+    kp.fused_finish = (W == 1); kp.world = W; kp.carry_best = 0;
+    kp.off_best = IN_CONTACT + 4 * H;
+    kp.off_sigma = kp.off_best + h->P;
+    kp.in_stride = (int)round4(kp.off_sigma + h->P);
+    kp.off_out_sigma = OUT_BEST + h->P;
+    kp.off_out_elite = OUT_BEST + 2 * h->P;
+    kp.out_stride = (int)round4(kp.off_out_elite + elite_k);
+    kp.blk_rec_stride = (int)round4(REC_V + h->P);
+    kp.shard_rec_stride = (int)round4(REC_V + h->P + 2 * elite_k);
+    kp.inv_m = 1.0f / cfg->mass;                                                    // M:118
+    kp.mg = (float)((double)cfg->mass * 9.81);                                      // S:380 (folded in double, then cast)
+    kp.mu = cfg->mu; kp.fz_min = cfg->grf_min; kp.fz_max = cfg->grf_max;
+    memcpy(kp.I, cfg->inertia, sizeof(kp.I));
+    inv3f(cfg->inertia, kp.Iinv);                                                   // M:56
+    memcpy(kp.qd, cfg->q_diag, sizeof(kp.qd));
+    kp.mpc_dt = cfg->dts[H - 1];                                                    // A:179: pgg mpc_dt = self.dt
+    kp.duty = cfg->pgg_duty_factor;
+    memcpy(kp.sigma_rs, cfg->sigma_random_sampling, sizeof(kp.sigma_rs));
+    kp.sigma_mppi = cfg->sigma_mppi;
+    memcpy(kp.freq_avail, cfg->step_freq_available, sizeof(kp.freq_avail));
+    kp.inv_ns = 1.0f / (float)ns;
+    const float denom_fixed = (float)((double)H / (double)ns);                     // horizon_leg / num_spline, S:191
+    kp.denom_fixed_inv = 1.0f / denom_fixed;
+    for (int i = 0; i <= ns; ++i) kp.bounds[i] = (float)((double)H * i / (double)ns);   // linspace(0,H,ns+1), S:187
+    for (int n = 0; n < H; ++n) {
+        kp.dt[n] = cfg->dts[n];
+        const float stepf = (float)n;
+        const int idx = cfg->parametrization == QPMPC_ZERO_ORDER ? 0 : chunk_index_host(cfg, stepf, kp.bounds);
+        kp.sp_index[n] = (unsigned char)idx;
+        const float q = stepf / denom_fixed - (float)idx;                           // S:191-194
+        if (cfg->parametrization == QPMPC_CUBIC_SPLINE) {                           // S:222-225
+            kp.basis[n][0] = 2.0f * q * q * q - 3.0f * q * q + 1.0f;
+            kp.basis[n][1] = (q * q * q - 2.0f * q * q + q) * 1.0f;
+            kp.basis[n][2] = -2.0f * q * q * q + 3.0f * q * q;
+            kp.basis[n][3] = (q * q * q - q * q) * 1.0f;
+        } else if (cfg->parametrization == QPMPC_LINEAR_SPLINE) {                   // S:197
+            kp.basis[n][0] = 1.0f - q; kp.basis[n][1] = q;
+        }
+    }
+    h->smem_bytes = smem_floats(kp.in_stride, h->P) * sizeof(float);
+    if (h->smem_bytes > 227 * 1024) { delete h; return fail(QPMPC_ERR_INVALID, "tile of %d knots needs %zu B shared memory (> 227 KB)", h->P, h->smem_bytes); }
+
+    h->tick_fn = g_tick_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+#define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
+    CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CKH(cudaEventCreate(&h->ev0));
+    CKH(cudaEventCreate(&h->ev1));
+    const size_t R = h->R;
+    const unsigned host_flags = cfg->io_mode == QPMPC_IO_MAPPED ? cudaHostAllocMapped : cudaHostAllocDefault;
+    CKH(cudaHostAlloc((void **)&h->h_in, R * kp.in_stride * sizeof(float), host_flags));
+    CKH(cudaHostAlloc((void **)&h->h_out, R * kp.out_stride * sizeof(float), host_flags));
+    CKH(cudaHostAlloc((void **)&h->h_rec, (size_t)W * R * kp.shard_rec_stride * sizeof(float), cudaHostAllocDefault));
+    memset(h->h_in, 0, R * kp.in_stride * sizeof(float));
+    memset(h->h_out, 0, R * kp.out_stride * sizeof(float));
+    CKH(cudaMalloc((void **)&h->d_in, R * kp.in_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_out, R * kp.out_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_costs, R * (size_t)h->N * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + TB - 1) / TB)) * kp.blk_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_send, R * kp.shard_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_recv, (size_t)W * R * kp.shard_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
+    CKH(cudaMalloc((void **)&h->d_sigma, (size_t)h->P * sizeof(float)));
+    CKH(cudaMemset(h->d_counters, 0, R * sizeof(unsigned int)));
+    CKH(cudaMemset(h->d_in, 0, R * kp.in_stride * sizeof(float)));
+    CKH(cudaMemset(h->d_out, 0, R * kp.out_stride * sizeof(float)));
+    if (cfg->io_mode == QPMPC_IO_MAPPED) {
+        CKH(cudaHostGetDevicePointer((void **)&h->kin, h->h_in, 0));
+        CKH(cudaHostGetDevicePointer((void **)&h->kout, h->h_out, 0));
+    } else {
+        h->kin = h->d_in; h->kout = h->d_out;
+    }
+    kp.in = h->kin; kp.out = h->kout; kp.costs = h->d_costs; kp.blk_recs = h->d_blk;
+    kp.shard_send = h->d_send; kp.shard_recv = h->d_recv; kp.counters = h->d_counters;
+    kp.noise = nullptr; kp.freqs = nullptr;
+    *out = h;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_num_parameters(const qpmpc_handle *h) { return h ? h->P : QPMPC_ERR_INVALID; }
+extern "C" int qpmpc_num_local_samples(const qpmpc_handle *h) { return h ? h->n_local : QPMPC_ERR_INVALID; }
+extern "C" int qpmpc_shard_record_floats(const qpmpc_handle *h) { return h ? h->R * h->kp.shard_rec_stride : QPMPC_ERR_INVALID; }
+
+// ------------------------------------------------------------------------------------------------------
+// packing / unpacking of the per-robot records
+// ------------------------------------------------------------------------------------------------------
+static inline float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explicit_params) {
+    const KParams &kp = h->kp;
+    float *rec = h->h_in + (size_t)r * kp.in_stride;
+    if (!in->state || !in->reference || !in->contact_sequence) return fail(QPMPC_ERR_INVALID, "state / reference / contact_sequence must not be NULL");
+    if (in->contact_ld < h->H) return fail(QPMPC_ERR_INVALID, "contact_ld %d < horizon %d", in->contact_ld, h->H);
+    memcpy(rec + IN_STATE, in->state, 24 * sizeof(float));
+    memcpy(rec + IN_REF, in->reference, 24 * sizeof(float));
+    for (int l = 0; l < 4; ++l) rec[IN_PHASE + l] = in->phase_signal ? in->phase_signal[l] : 0.f;
+    if (h->cfg.adaptive && !in->phase_signal) return fail(QPMPC_ERR_INVALID, "phase_signal is required by the gait-adaptive controller");
+    rec[IN_NOMFREQ] = in->nominal_step_freq;
+    rec[IN_OPTSWING] = u2f((uint32_t)in->optimize_swing);
+    rec[IN_SEED] = u2f(in->key[0]);
+    rec[IN_TICK] = u2f(in->key[1]);
+    rec[IN_ROBOT] = u2f((uint32_t)r);
+    for (int l = 0; l < 4; ++l)
+        for (int n = 0; n < h->H; ++n) {
+            const float c = in->contact_sequence[(size_t)l * in->contact_ld + n];
+            if (c != 0.0f && c != 1.0f) return fail(QPMPC_ERR_INVALID, "contact_sequence[%d][%d] = %g is not 0 or 1", l, n, (double)c);
+            rec[IN_CONTACT + l * h->H + n] = c;
+        }
+    float *best = rec + kp.off_best, *sigma = rec + kp.off_sigma;
+    if (explicit_params || !in->best) memset(best, 0, h->P * sizeof(float));
+    else memcpy(best, in->best, h->P * sizeof(float));
+    if (h->cfg.method == QPMPC_CEM_MPPI && !explicit_params) {
+        if (!in->sigma) return fail(QPMPC_ERR_INVALID, "sigma is required by cem_mppi");
+        memcpy(sigma, in->sigma, h->P * sizeof(float));
+    } else memset(sigma, 0, h->P * sizeof(float));
+    return QPMPC_OK;
+}
+
+static void unpack_one(const qpmpc_handle *h, int r, const float *base, qpmpc_tick_out *out) {
+    const KParams &kp = h->kp;
+    const float *rec = base + (size_t)r * kp.out_stride;
+    memcpy(out->grfs, rec + OUT_GRF, 12 * sizeof(float));
+    memcpy(out->predicted_state, rec + OUT_PRED, 24 * sizeof(float));
+    out->best_cost = rec[OUT_BESTCOST];
+    out->best_freq = rec[OUT_BESTFREQ];
+    out->best_index = (int32_t)f2u(rec[OUT_BESTIDX]);
+    out->num_elite = (int32_t)f2u(rec[OUT_NELITE]);
+    if (out->best) memcpy(out->best, rec + OUT_BEST, h->P * sizeof(float));
+    if (out->sigma_new && h->cfg.method == QPMPC_CEM_MPPI) memcpy(out->sigma_new, rec + kp.off_out_sigma, h->P * sizeof(float));
+    if (out->elite_indices && kp.elite_k > 0) memcpy(out->elite_indices, rec + kp.off_out_elite, kp.elite_k * sizeof(int32_t));
+}
+
+static int ensure_noise(qpmpc_handle *h, size_t floats) {
+    if (h->noise_capacity >= floats) return QPMPC_OK;
+    cudaFree(h->d_noise); h->d_noise = nullptr; h->noise_capacity = 0;
+    CK(cudaMalloc((void **)&h->d_noise, floats * sizeof(float)));
+    h->noise_capacity = floats;
+    return QPMPC_OK;
+}
+static int ensure_freqs(qpmpc_handle *h, size_t floats) {
+    if (h->freqs_capacity >= floats) return QPMPC_OK;
+    cudaFree(h->d_freqs); h->d_freqs = nullptr; h->freqs_capacity = 0;
+    CK(cudaMalloc((void **)&h->d_freqs, floats * sizeof(float)));
+    h->freqs_capacity = floats;
+    return QPMPC_OK;
+}
+
+static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid) {
+    void *args[] = {(void *)&kp};
+    CK(cudaLaunchKernel((const void *)fn, grid, dim3(TB), args, h->smem_bytes, h->stream));
+    h->launches++;
+    return QPMPC_OK;
+}
+
+// upload injected noise / freqs of all robots if any is present; fills kp accordingly
+static int stage_injection(qpmpc_handle *h, const qpmpc_tick_in *in, int count, KParams &kp) {
+    bool any_noise = false, any_freq = false;
+    for (int r = 0; r < count; ++r) { any_noise |= (in[r].noise != nullptr); any_freq |= (in[r].step_freqs != nullptr); }
+    if (any_noise) {
+        const size_t per = (size_t)h->N * h->P;
+        int rc = ensure_noise(h, per * count);
+        if (rc) return rc;
+        for (int r = 0; r < count; ++r) {
+            if (!in[r].noise) return fail(QPMPC_ERR_INVALID, "noise injected for some robots but not robot %d", r);
+            CK(cudaMemcpyAsync(h->d_noise + per * r, in[r].noise, per * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        }
+        kp.noise_mode = NOISE_INJECTED; kp.noise = h->d_noise;
+    }
+    if (any_freq) {
+        int rc = ensure_freqs(h, (size_t)h->N * count);
+        if (rc) return rc;
+        for (int r = 0; r < count; ++r) {
+            if (!in[r].step_freqs) return fail(QPMPC_ERR_INVALID, "step_freqs injected for some robots but not robot %d", r);
+            CK(cudaMemcpyAsync(h->d_freqs + (size_t)h->N * r, in[r].step_freqs, (size_t)h->N * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        }
+        kp.freq_injected = 1; kp.freqs = h->d_freqs;
+    }
+    return QPMPC_OK;
+}
+
+static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
+    if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: use qpmpc_tick_sharded / qpmpc_shard_partial");
+    CK(cudaSetDevice(h->cfg.device));
+    const int R = h->R;
+    for (int r = 0; r < R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
+    KParams kp = h->kp;
+    int rc = stage_injection(h, in, R, kp);
+    if (rc) return rc;
+    const bool plain = (kp.noise_mode == NOISE_PHILOX && !kp.freq_injected);
+    const size_t in_bytes = (size_t)R * kp.in_stride * sizeof(float), out_bytes = (size_t)R * kp.out_stride * sizeof(float);
+    const dim3 grid(kp.nblk, R);
+    const bool mapped = h->cfg.io_mode == QPMPC_IO_MAPPED;
+    if (plain && h->cfg.use_graph && !mapped) {
+        if (!h->graph_exec) {                      // capture (H2D, kernel, D2H) once; the packet addresses never change
+            cudaGraph_t g = nullptr;
+            CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+            cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, h->stream);
+            void *args[] = {(void *)&kp};
+            cudaLaunchKernel((const void *)h->tick_fn, grid, dim3(TB), args, h->smem_bytes, h->stream);
+            cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream);
+            CK(cudaStreamEndCapture(h->stream, &g));
+            CK(cudaGraphInstantiate(&h->graph_exec, g, 0));
+            CK(cudaGraphDestroy(g));
+        }
+        CK(cudaGraphLaunch(h->graph_exec, h->stream));
+        h->launches++;
+    } else {
+        if (!mapped) CK(cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        rc = launch(h, h->tick_fn, kp, grid);
+        if (rc) return rc;
+        if (!mapped) CK(cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
+    if (h && h->R != 1) return fail(QPMPC_ERR_INVALID, "handle batches %d robots: use qpmpc_tick_batched", h->R);
+    return run_tick(h, in, out);
+}
+extern "C" int qpmpc_tick_batched(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) { return run_tick(h, in, out); }
+
+extern "C" int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst) {
+    if (!h || !dst || robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "bad argument");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaMemcpyAsync(dst, h->d_costs + (size_t)robot * h->n_local, (size_t)h->n_local * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_rollout(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                             int32_t contact_ld, const float *phase_signal, const float *params, const float *step_freqs,
+                             float *costs) {
+    if (!h || !params || !costs) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (h->R != 1) return fail(QPMPC_ERR_INVALID, "qpmpc_rollout needs a single-robot handle");
+    if (h->cfg.adaptive && !step_freqs) return fail(QPMPC_ERR_INVALID, "step_freqs is required by the gait-adaptive rollout (A:326)");
+    CK(cudaSetDevice(h->cfg.device));
+    qpmpc_tick_in in;
+    memset(&in, 0, sizeof(in));
+    in.state = state; in.reference = reference; in.contact_sequence = contact_sequence; in.contact_ld = contact_ld;
+    in.phase_signal = phase_signal;
+    int rc = pack_one(h, 0, &in, true);
+    if (rc) return rc;
+    KParams kp = h->kp;
+    kp.mode = MODE_ROLLOUT; kp.n_local = h->N; kp.sample_base = 0; kp.fused_finish = 0;
+    plan_blocks(h->N, &kp.iters, &kp.nblk);
+    const size_t per = (size_t)h->N * h->P;
+    rc = ensure_noise(h, per);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h->d_noise, params, per * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    kp.noise_mode = NOISE_INJECTED; kp.noise = h->d_noise;
+    if (step_freqs) {
+        rc = ensure_freqs(h, h->N);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->d_freqs, step_freqs, (size_t)h->N * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        kp.freq_injected = 1; kp.freqs = h->d_freqs;
+    }
+    float *din = h->d_in;
+    CK(cudaMemcpyAsync(din, h->h_in, (size_t)kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    kp.in = din;
+    rc = launch(h, h->tick_fn, kp, dim3(kp.nblk, 1));
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(costs, h->d_costs, (size_t)h->N * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_generate_noise(qpmpc_handle *h, int robot, const uint32_t key[2], const float *sigma, float *dst) {
+    if (!h || !key || !dst) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (h->cfg.method == QPMPC_CEM_MPPI && !sigma) return fail(QPMPC_ERR_INVALID, "sigma is required by cem_mppi");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t per = (size_t)h->N * h->P;
+    int rc = ensure_noise(h, per);
+    if (rc) return rc;
+    if (sigma) CK(cudaMemcpyAsync(h->d_sigma, sigma, (size_t)h->P * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    const int threads = 256;
+    const int blocks = (int)std::min<size_t>((per / 4 + threads - 1) / threads, 148 * 8);
+    switch (h->cfg.method) {
+        case QPMPC_RANDOM_SAMPLING: noise_export_kernel<RANDOM_SAMPLING><<<blocks, threads, 0, h->stream>>>(h->kp, key[0], (uint32_t)robot, key[1], h->d_sigma, h->d_noise); break;
+        case QPMPC_MPPI: noise_export_kernel<MPPI><<<blocks, threads, 0, h->stream>>>(h->kp, key[0], (uint32_t)robot, key[1], h->d_sigma, h->d_noise); break;
+        default: noise_export_kernel<CEM_MPPI><<<blocks, threads, 0, h->stream>>>(h->kp, key[0], (uint32_t)robot, key[1], h->d_sigma, h->d_noise); break;
+    }
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, h->d_noise, per * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_generate_step_freqs(qpmpc_handle *h, int robot, const uint32_t key[2], float nominal_step_freq,
+                                         int32_t optimize_swing, float *dst) {
+    if (!h || !key || !dst) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = ensure_freqs(h, h->N);
+    if (rc) return rc;
+    float *rec = h->h_in;                        // scratch use of robot 0's packet (overwritten by the next tick anyway)
+    rec[IN_NOMFREQ] = nominal_step_freq; rec[IN_OPTSWING] = u2f((uint32_t)optimize_swing);
+    rec[IN_SEED] = u2f(key[0]); rec[IN_TICK] = u2f(key[1]); rec[IN_ROBOT] = u2f((uint32_t)robot);
+    CK(cudaMemcpyAsync(h->d_in, rec, (size_t)h->kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    KParams kp = h->kp;
+    kp.freq_injected = 0;
+    const int threads = 256, blocks = std::min((h->N + threads - 1) / threads, 148 * 8);
+    switch (h->cfg.method) {
+        case QPMPC_RANDOM_SAMPLING: freq_export_kernel<RANDOM_SAMPLING><<<blocks, threads, 0, h->stream>>>(kp, h->d_in, h->d_freqs); break;
+        case QPMPC_MPPI: freq_export_kernel<MPPI><<<blocks, threads, 0, h->stream>>>(kp, h->d_in, h->d_freqs); break;
+        default: freq_export_kernel<CEM_MPPI><<<blocks, threads, 0, h->stream>>>(kp, h->d_in, h->d_freqs); break;
+    }
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, h->d_freqs, (size_t)h->N * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// sample-sharded controller: partial -> (NCCL all-gather | caller-side gather) -> finish
+// ------------------------------------------------------------------------------------------------------
+static int shard_partial_async(qpmpc_handle *h, const qpmpc_tick_in *in, KParams &kp) {
+    const int R = h->R;
+    for (int r = 0; r < R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
+    kp = h->kp;
+    kp.fused_finish = 0;
+    int rc = stage_injection(h, in, R, kp);
+    if (rc) return rc;
+    if (h->cfg.io_mode != QPMPC_IO_MAPPED)
+        CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)R * kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    return launch(h, h->tick_fn, kp, dim3(kp.nblk, R));
+}
+
+static int shard_finish_async(qpmpc_handle *h, const KParams &kp_in) {
+    KParams kp = kp_in;
+    int rc = launch(h, h->finish_fn, kp, dim3(1, h->R));
+    if (rc) return rc;
+    if (h->cfg.io_mode != QPMPC_IO_MAPPED)
+        CK(cudaMemcpyAsync(h->h_out, h->d_out, (size_t)h->R * kp.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    return QPMPC_OK;
+}
+
+static thread_local KParams g_partial_kp;   // noise/freq injection state carried from partial to finish
+
+extern "C" int qpmpc_shard_partial(qpmpc_handle *h, const qpmpc_tick_in *in) {
+    if (!h || !in) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = shard_partial_async(h, in, g_partial_kp);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    h->partial_done = true;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_record_device_ptr(qpmpc_handle *h, void **send, void **recv) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    if (send) *send = h->d_send;
+    if (recv) *recv = h->d_recv;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_get_record(qpmpc_handle *h, float *host_rec) {
+    if (!h || !host_rec) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaMemcpy(host_rec, h->d_send, (size_t)h->R * h->kp.shard_rec_stride * sizeof(float), cudaMemcpyDeviceToHost));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_copy_record(qpmpc_handle *h, int slot, const float *host_rec) {
+    if (!h || !host_rec || slot < 0 || slot >= h->cfg.shard_world) return fail(QPMPC_ERR_INVALID, "bad argument");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t n = (size_t)h->R * h->kp.shard_rec_stride;
+    CK(cudaMemcpy(h->d_recv + n * slot, host_rec, n * sizeof(float), cudaMemcpyHostToDevice));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_finish(qpmpc_handle *h, qpmpc_tick_out *out) {
+    if (!h || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h->partial_done) return fail(QPMPC_ERR_STATE, "qpmpc_shard_finish without a preceding qpmpc_shard_partial");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = shard_finish_async(h, g_partial_kp);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < h->R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    h->partial_done = false;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_nccl_unique_id(const char *libnccl_path, unsigned char id[128]) {
+    int rc = load_nccl(libnccl_path);
+    if (rc) return rc;
+    NcclId nid;
+    int e = g_nccl.GetUniqueId(&nid);
+    if (e != 0) return fail(QPMPC_ERR_NCCL, "ncclGetUniqueId: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "error");
+    memcpy(id, nid.internal, 128);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_init_nccl(qpmpc_handle *h, const char *libnccl_path, const unsigned char id[128]) {
+    if (!h || !id) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    int rc = load_nccl(libnccl_path);
+    if (rc) return rc;
+    CK(cudaSetDevice(h->cfg.device));
+    NcclId nid;
+    memcpy(nid.internal, id, 128);
+    int e = g_nccl.CommInitRank(&h->comm, h->cfg.shard_world, nid, h->cfg.shard_rank);
+    if (e != 0) return fail(QPMPC_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "error");
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
+    if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h->comm) return fail(QPMPC_ERR_STATE, "qpmpc_shard_init_nccl has not been called");
+    CK(cudaSetDevice(h->cfg.device));
+    KParams kp;
+    int rc = shard_partial_async(h, in, kp);
+    if (rc) return rc;
+    const size_t n = (size_t)h->R * kp.shard_rec_stride;
+    int e = g_nccl.AllGather(h->d_send, h->d_recv, n, /*ncclFloat32*/ 7, h->comm, h->stream);   // one small collective per tick
+    if (e != 0) return fail(QPMPC_ERR_NCCL, "ncclAllGather: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "error");
+    rc = shard_finish_async(h, kp);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < h->R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    return QPMPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// device-resident benchmarking helpers
+// ------------------------------------------------------------------------------------------------------
+extern "C" int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in) {
+    if (!h || !in) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    for (int r = 0; r < h->R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
+    CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)h->R * h->kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->resident_uploaded = true;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms) {
+    if (!h || !ms || steps < 1) return fail(QPMPC_ERR_INVALID, "bad argument");
+    if (!h->resident_uploaded) return fail(QPMPC_ERR_STATE, "qpmpc_upload_resident has not been called");
+    if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "resident benchmarking needs an unsharded handle");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t flush_bytes = (size_t)256 << 20;            // > 126 MB L2
+    if (flush_l2 && !h->d_flush) CK(cudaMalloc((void **)&h->d_flush, flush_bytes));
+    KParams kp = h->kp;
+    kp.in = h->d_in; kp.out = h->d_out;                      // inputs / outputs stay in HBM
+    const dim3 grid(kp.nblk, h->R);
+    for (int i = 0; i < steps; ++i) {
+        if (flush_l2) CK(cudaMemsetAsync(h->d_flush, i & 0xff, flush_bytes, h->stream));
+        CK(cudaEventRecord(h->ev0, h->stream));
+        int rc = launch(h, h->tick_fn, kp, grid);
+        if (rc) return rc;
+        CK(cudaEventRecord(h->ev1, h->stream));
+        CK(cudaEventSynchronize(h->ev1));
+        CK(cudaEventElapsedTime(&ms[i], h->ev0, h->ev1));
+    }
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_fetch_resident_out(qpmpc_handle *h, qpmpc_tick_out *out) {
+    if (!h || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    std::vector<float> tmp((size_t)h->R * h->kp.out_stride);
+    CK(cudaMemcpy(tmp.data(), h->d_out, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (int r = 0; r < h->R; ++r) unpack_one(h, r, tmp.data(), &out[r]);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_kernel_launch_count(const qpmpc_handle *h, uint64_t *count) {
+    if (!h || !count) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    *count = h->launches;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_measure_fp32_peak(int device, float *tflops) {
+    if (!tflops) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    int ndev = 0;
+    int rc = qpmpc_device_count(&ndev);
+    if (rc) return rc;
+    if (device < 0 || device >= ndev) return fail(QPMPC_ERR_INVALID, "device %d out of range", device);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    const int threads = 256, blocks = prop.multiProcessorCount * 8, iters = 4096;
+    float *d = nullptr;
+    CK(cudaMalloc((void **)&d, (size_t)threads * blocks * sizeof(float)));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 0.f;
+    for (int rep = 0; rep < 6; ++rep) {
+        CK(cudaEventRecord(e0));
+        fp32_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 1e-3f);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double flop = (double)threads * blocks * (double)iters * 16.0 * 8.0 * 2.0;
+        const float tf = (float)(flop / (ms * 1e-3) / 1e12);
+        if (rep > 0 && tf > best) best = tf;
+    }
+    CK(cudaGetLastError());
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = best;
+    return QPMPC_OK;
+}

@@ -1,0 +1,585 @@
+// qpmpc_kernels.cuh -- device code of libqpmpc_b200 (sm_100a).
+//
+// One fused launch per MPC tick:  noise (Philox4x32-10, or an injected tensor)  ->  perturb  ->  spline  ->
+// clamp -> SRBD explicit-Euler rollout + cost with the horizon loop in registers -> block-level
+// (min, argmin) / online-softmax (m, s, sum w*eps) partials -> last-block-done merge -> MPPI/CEM update ->
+// GRF read-out + predicted state.   grid = (blocks per robot, robots), one sample per thread per tile.
+//
+// Reference lines restated here (paths relative to the reference's quadruped_pympc/):
+//   S = controllers/sampling/centroidal_nmpc_jax.py, M = controllers/sampling/centroidal_model_jax.py,
+//   A = controllers/sampling/centroidal_nmpc_jax_gait_adaptive.py, G = helpers/periodic_gait_generator_jax.py
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace qp {
+
+constexpr int TB = 128;          // threads per block = samples per tile
+constexpr int TS = TB + 1;       // tile row stride (floats): bank = (p + t) % 32 for both access patterns
+constexpr int MAX_H = 64;
+constexpr int MAX_NS = 16;
+constexpr int MAX_ELITE = 256;
+
+enum { ZERO_ORDER = 0, LINEAR = 1, CUBIC = 2 };
+enum { RANDOM_SAMPLING = 0, MPPI = 1, CEM_MPPI = 2 };
+enum { MODE_TICK = 0, MODE_ROLLOUT = 2 };             // MODE_ROLLOUT: explicit params in, raw costs out
+enum { NOISE_PHILOX = 0, NOISE_INJECTED = 1 };
+
+// ---- per-robot input record (floats), written by the host ------------------------------------------------
+enum { IN_STATE = 0, IN_REF = 24, IN_PHASE = 48, IN_NOMFREQ = 52, IN_OPTSWING = 53, IN_SEED = 54, IN_TICK = 55,
+       IN_ROBOT = 56, IN_CONTACT = 60 };              // contact: 4 x H ; then best (P) ; then sigma (P)
+// ---- per-robot output record -------------------------------------------------------------------------------
+enum { OUT_GRF = 0, OUT_PRED = 12, OUT_BESTCOST = 36, OUT_BESTFREQ = 37, OUT_BESTIDX = 38, OUT_NELITE = 39,
+       OUT_BEST = 40 };                               // then sigma_new (P) ; then elite indices (elite_k ints)
+// ---- block / shard record -------------------------------------------------------------------------------------
+enum { REC_M = 0, REC_IDX = 1, REC_S = 2, REC_PAD = 3, REC_V = 4 };   // then V (P) ; shard: then top-k (cost, idx) pairs
+
+struct KParams {
+    int N;             // samples of the whole controller (global)
+    int n_local;       // samples evaluated by this launch (this shard)
+    int sample_base;   // global index of this shard's first sample
+    int H, ns, P, P_leg;
+    int iters;         // tiles per block
+    int nblk;          // blocks per robot
+    int elite_k;
+    int mode;          // MODE_TICK | MODE_ROLLOUT
+    int noise_mode;    // NOISE_PHILOX | NOISE_INJECTED
+    int freq_injected; // 1: per-sample step frequencies come from `freqs`
+    int fused_finish;  // 1: the last block also merges the (single) shard record and writes `out`
+    int world;         // shard records to merge in finish
+    int carry_best;    // 1: write best_new back into the input record (device-resident multi-tick runs)
+    int off_best, off_sigma, in_stride;
+    int off_out_sigma, off_out_elite, out_stride;
+    int blk_rec_stride, shard_rec_stride;
+    float inv_m, mg, mu, fz_min, fz_max;
+    float I[9], Iinv[9];
+    float qd[12];
+    float mpc_dt, duty;
+    float sigma_rs[3], sigma_mppi;
+    float freq_avail[3];
+    float inv_ns, denom_fixed_inv;          // 1/ns ; 1/(H/ns)
+    float dt[MAX_H];
+    float basis[MAX_H][4];                  // fixed gait: cubic (a,b,c,d) | linear (1-q, q, -, -) per step
+    float bounds[MAX_NS + 1];               // linspace(0,H,ns+1), S:187
+    unsigned char sp_index[MAX_H];          // fixed gait: spline chunk index per step, S:189
+    const float *in;                        // [R][in_stride]
+    float *out;                             // [R][out_stride]
+    float *costs;                           // [R][n_local]
+    float *blk_recs;                        // [R][nblk][blk_rec_stride]
+    float *shard_send;                      // [R][shard_rec_stride]  (this shard's record)
+    const float *shard_recv;                // [world][R][shard_rec_stride]
+    unsigned int *counters;                 // [R]
+    const float *noise;                     // injected: [R][N][P] (additional noise, or explicit params in MODE_ROLLOUT)
+    const float *freqs;                     // injected: [R][N]
+};
+
+// ======================================================================================================
+// RNG: Philox4x32-10, counter = (quad, row, tick, stream), key = (seed, robot)   (host mirror: oracle/sampling_oracle.c)
+// ======================================================================================================
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+__device__ __forceinline__ float u01_from_bits(uint32_t b) { return __uint_as_float((b >> 9) | 0x3F800000u) - 1.0f; }
+
+// Giles' single-precision erfinv (the polynomial XLA's erf_inv lowers to); central branch |x| < 0.9966
+__device__ __forceinline__ float erfinv_giles(float x) {
+    float w = -__logf((1.0f - x) * (1.0f + x));
+    float p;
+    if (w < 5.0f) {
+        w = w - 2.5f;
+        p = 2.81022636e-08f;
+        p = fmaf(p, w, 3.43273939e-07f);
+        p = fmaf(p, w, -3.5233877e-06f);
+        p = fmaf(p, w, -4.39150654e-06f);
+        p = fmaf(p, w, 0.00021858087f);
+        p = fmaf(p, w, -0.00125372503f);
+        p = fmaf(p, w, -0.00417768164f);
+        p = fmaf(p, w, 0.246640727f);
+        p = fmaf(p, w, 1.50140941f);
+    } else {
+        w = sqrtf(w) - 3.0f;
+        p = -0.000200214257f;
+        p = fmaf(p, w, 0.000100950558f);
+        p = fmaf(p, w, 0.00134934322f);
+        p = fmaf(p, w, -0.00367342844f);
+        p = fmaf(p, w, 0.00573950773f);
+        p = fmaf(p, w, -0.0076224613f);
+        p = fmaf(p, w, 0.00943887047f);
+        p = fmaf(p, w, 1.00167406f);
+        p = fmaf(p, w, 2.83297682f);
+    }
+    return p * x;
+}
+
+// jax.random.normal's construction: sqrt(2) * erfinv(uniform(nextafter(-1,0), 1))
+__device__ __forceinline__ float normal_from_bits(uint32_t b) {
+    const float lo = -0.99999994f;
+    float u = fmaf(u01_from_bits(b), 2.0f, lo);
+    u = u > lo ? u : lo;
+    return 1.41421356f * erfinv_giles(u);
+}
+
+// One quad (4 consecutive knots) of additional_random_parameters for global row i.
+//  random_sampling S:647-677: rows [1,1+k) s0*N, [1+k,1+2k) s1*N (same key => same normals), [1+2k,N) U(-s2,s2)
+//  mppi S:806-812: s*N on rows 1..N-1 ; cem_mppi S:951-958: N*sigma[p] ; row 0 is always zero.
+template <int METHOD>
+__device__ __forceinline__ float4 noise_quad(const KParams &kp, uint32_t seed, uint32_t robot, uint32_t tick, int i,
+                                             int q, const float *s_sigma) {
+    if (i == 0) return make_float4(0.f, 0.f, 0.f, 0.f);
+    int seg = 0, j = i - 1;
+    if (METHOD == RANDOM_SAMPLING) {
+        const int k = kp.N / 3;
+        if (i >= 1 + 2 * k) { seg = 2; j = i - 1 - 2 * k; }
+        else if (i >= 1 + k) { seg = 1; j = i - 1 - k; }
+    }
+    uint4 r = philox4x32_10((uint32_t)q, (uint32_t)j, tick, 0u, seed, robot);
+    float4 v;
+    if (METHOD == RANDOM_SAMPLING) {
+        if (seg == 2) {
+            const float s2 = kp.sigma_rs[2];
+            const float span = s2 - (-s2);
+            v.x = fmaxf(fmaf(u01_from_bits(r.x), span, -s2), -s2);
+            v.y = fmaxf(fmaf(u01_from_bits(r.y), span, -s2), -s2);
+            v.z = fmaxf(fmaf(u01_from_bits(r.z), span, -s2), -s2);
+            v.w = fmaxf(fmaf(u01_from_bits(r.w), span, -s2), -s2);
+        } else {
+            const float s = kp.sigma_rs[seg];
+            v.x = s * normal_from_bits(r.x); v.y = s * normal_from_bits(r.y);
+            v.z = s * normal_from_bits(r.z); v.w = s * normal_from_bits(r.w);
+        }
+    } else if (METHOD == MPPI) {
+        const float s = kp.sigma_mppi;
+        v.x = s * normal_from_bits(r.x); v.y = s * normal_from_bits(r.y);
+        v.z = s * normal_from_bits(r.z); v.w = s * normal_from_bits(r.w);
+    } else {
+        v.x = normal_from_bits(r.x) * s_sigma[4 * q + 0]; v.y = normal_from_bits(r.y) * s_sigma[4 * q + 1];
+        v.z = normal_from_bits(r.z) * s_sigma[4 * q + 2]; v.w = normal_from_bits(r.w) * s_sigma[4 * q + 3];
+    }
+    return v;
+}
+
+// Per-sample step frequency (row a15).  A:688-692 (random_sampling) | A:835-838 (mppi) | A:994-1000 (cem_mppi)
+template <int METHOD>
+__device__ __forceinline__ float sample_step_freq(const KParams &kp, const float *s_in, int robot_slot, int i) {
+    if (kp.freq_injected) return __ldg(kp.freqs + (size_t)robot_slot * kp.N + i);
+    const uint32_t seed = __float_as_uint(s_in[IN_SEED]), tick = __float_as_uint(s_in[IN_TICK]);
+    const uint32_t robot = __float_as_uint(s_in[IN_ROBOT]);
+    uint4 r = philox4x32_10(0u, (uint32_t)i, tick, 1u, seed, robot);
+    const int c = (int)__umulhi(r.x, 3u);
+    const float nominal = s_in[IN_NOMFREQ];
+    const int opt = __float_as_int(s_in[IN_OPTSWING]);
+    if (METHOD == RANDOM_SAMPLING) return opt ? kp.freq_avail[c] : nominal;
+    if (METHOD == MPPI) return kp.freq_avail[c];
+    const float inc = (c == 0) ? 0.0f : (c == 1 ? 0.2f : 0.4f);
+    return fmaf(inc, (float)opt, nominal);
+}
+
+// ======================================================================================================
+// SRBD: M:93-174 (fd + explicit Euler) and the cost S:450-451, one step, state in registers
+// ======================================================================================================
+struct Body { float px, py, pz, vx, vy, vz, roll, pitch, yaw, wx, wy, wz; };
+
+// S:270-314 (box friction pyramid, same comparison order; NaN fz -> fz_min)
+__device__ __forceinline__ void clamp_leg(const KParams &kp, float &fx, float &fy, float &fz) {
+    fz = fz > kp.fz_min ? fz : kp.fz_min;
+    fz = fz < kp.fz_max ? fz : kp.fz_max;
+    const float lo = -kp.mu * fz, hi = kp.mu * fz;
+    fx = fx > lo ? fx : lo; fx = fx < hi ? fx : hi;
+    fy = fy > lo ? fy : lo; fy = fy < hi ? fy : hi;
+}
+
+// Fx..: sum of stance forces; tx..: sum of (foot - com) x F (world frame), M:111-118,132-135
+__device__ __forceinline__ float srbd_step(const KParams &kp, Body &b, float Fx, float Fy, float Fz, float tx, float ty,
+                                           float tz, float dt, const float *ref) {
+    const float ax = kp.inv_m * Fx, ay = kp.inv_m * Fy, az = fmaf(kp.inv_m, Fz, -9.81f);       // M:118
+    float sr, cr, sp, cp, sy, cy;
+    sincosf(b.roll, &sr, &cr);
+    sincosf(b.pitch, &sp, &cp);
+    sincosf(b.yaw, &sy, &cy);
+    // inverse of the conjugate Euler-rate matrix by cofactors with its structural zeros dropped, M:124-130,137
+    const float det = (cp * cr) * cr + sr * (cp * sr);
+    const float rd = 1.0f / det;
+    const float e01 = (sr * sp) * rd, e02 = (cr * sp) * rd, e11 = (cp * cr) * rd, e12 = -(cp * sr) * rd;
+    const float e21 = sr * rd, e22 = cr * rd;
+    const float droll = b.wx + e01 * b.wy + e02 * b.wz;
+    const float dpitch = e11 * b.wy + e12 * b.wz;
+    const float dyaw = e21 * b.wy + e22 * b.wz;
+    // b_R_w (ZYX), M:141-155, applied to the world torque
+    const float r00 = cp * cy, r01 = cp * sy, r02 = -sp;
+    const float r10 = sr * sp * cy - cr * sy, r11 = sr * sp * sy + cr * cy, r12 = sr * cp;
+    const float r20 = cr * sp * cy + sr * sy, r21 = cr * sp * sy - sr * cy, r22 = cr * cp;
+    const float bx = r00 * tx + r01 * ty + r02 * tz;
+    const float by = r10 * tx + r11 * ty + r12 * tz;
+    const float bz = r20 * tx + r21 * ty + r22 * tz;
+    // angular acceleration Iinv * (b_R_w tau - w x (I w)), M:157-159
+    const float Iwx = kp.I[0] * b.wx + kp.I[1] * b.wy + kp.I[2] * b.wz;
+    const float Iwy = kp.I[3] * b.wx + kp.I[4] * b.wy + kp.I[5] * b.wz;
+    const float Iwz = kp.I[6] * b.wx + kp.I[7] * b.wy + kp.I[8] * b.wz;
+    const float hx = bx - (b.wy * Iwz - b.wz * Iwy);
+    const float hy = by - (b.wz * Iwx - b.wx * Iwz);
+    const float hz = bz - (b.wx * Iwy - b.wy * Iwx);
+    const float dwx = kp.Iinv[0] * hx + kp.Iinv[1] * hy + kp.Iinv[2] * hz;
+    const float dwy = kp.Iinv[3] * hx + kp.Iinv[4] * hy + kp.Iinv[5] * hz;
+    const float dwz = kp.Iinv[6] * hx + kp.Iinv[7] * hy + kp.Iinv[8] * hz;
+    // explicit Euler, M:171-172 (all derivatives from the old state)
+    b.px = fmaf(b.vx, dt, b.px); b.py = fmaf(b.vy, dt, b.py); b.pz = fmaf(b.vz, dt, b.pz);
+    b.vx = fmaf(ax, dt, b.vx); b.vy = fmaf(ay, dt, b.vy); b.vz = fmaf(az, dt, b.vz);
+    b.roll = fmaf(droll, dt, b.roll); b.pitch = fmaf(dpitch, dt, b.pitch); b.yaw = fmaf(dyaw, dt, b.yaw);
+    b.wx = fmaf(dwx, dt, b.wx); b.wy = fmaf(dwy, dt, b.wy); b.wz = fmaf(dwz, dt, b.wz);
+    // e^T Q e on the state after the step, S:450-451 (only the non-zero diagonal entries of Q)
+    float e, c;
+    e = b.pz - ref[2]; c = (e * kp.qd[2]) * e;
+    e = b.vx - ref[3]; c = fmaf(e * kp.qd[3], e, c);
+    e = b.vy - ref[4]; c = fmaf(e * kp.qd[4], e, c);
+    e = b.vz - ref[5]; c = fmaf(e * kp.qd[5], e, c);
+    e = b.roll - ref[6]; c = fmaf(e * kp.qd[6], e, c);
+    e = b.pitch - ref[7]; c = fmaf(e * kp.qd[7], e, c);
+    e = b.wx - ref[9]; c = fmaf(e * kp.qd[9], e, c);
+    e = b.wy - ref[10]; c = fmaf(e * kp.qd[10], e, c);
+    e = b.wz - ref[11]; c = fmaf(e * kp.qd[11], e, c);
+    // the reference's Q also weights x, y (0), yaw (0): included so non-default q_diag stays exact
+    e = b.px - ref[0]; c = fmaf(e * kp.qd[0], e, c);
+    e = b.py - ref[1]; c = fmaf(e * kp.qd[1], e, c);
+    e = b.yaw - ref[8]; c = fmaf(e * kp.qd[8], e, c);
+    return c;
+}
+
+__device__ __forceinline__ Body load_body(const float *s) {
+    Body b;
+    b.px = s[0]; b.py = s[1]; b.pz = s[2]; b.vx = s[3]; b.vy = s[4]; b.vz = s[5];
+    b.roll = s[6]; b.pitch = s[7]; b.yaw = s[8]; b.wx = s[9]; b.wy = s[10]; b.wz = s[11];
+    return b;
+}
+
+// knot j of leg l for the thread whose tile column is `tcol`: best + eps  (S:680 | S:814 | S:960)
+#define QP_KNOT(l, j) (s_best[(l) * kp.P_leg + (j)] + tcol[((l) * kp.P_leg + (j)) * TS])
+
+__device__ __forceinline__ void add_leg(const KParams &kp, const Body &b, const float *foot, float fx, float fy, float fz,
+                                        float &Fx, float &Fy, float &Fz, float &tx, float &ty, float &tz) {
+    const float rx = foot[0] - b.px, ry = foot[1] - b.py, rz = foot[2] - b.pz;
+    Fx += fx; Fy += fy; Fz += fz;
+    tx += ry * fz - rz * fy;
+    ty += rz * fx - rx * fz;
+    tz += rx * fy - ry * fx;
+}
+
+// Fixed-gait rollout (S:316-496): every leg's spline clock is the step n, contact table shared by all samples,
+// so the swing/stance branch is block-uniform and swing legs are skipped (their force is multiplied by 0 twice,
+// S:388-402 and M:111-116).  s_fref[n] = mass*9.81 / n_stance(n) (S:377-380).
+template <int PARAM>
+__device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s_in, const float *s_fref, const float *tcol) {
+    const float *s_best = s_in + kp.off_best;
+    const float *s_contact = s_in + IN_CONTACT;
+    const float *ref = s_in + IN_REF;
+    const float *feet = s_in + IN_STATE + 12;
+    Body b = load_body(s_in + IN_STATE);
+    float cost = 0.0f;
+    const int H = kp.H;
+    constexpr float third = 1.0f / 3.0f;   // forces_z / forces_x = 30/10, S:388
+    // hoisted knots of the current spline chunk (cubic: k1, phi, k2, phi_next ; linear: k0, k1)
+    float ka[4][3], kb[4][3], kc[4][3], kd[4][3];
+    int cur = -1;
+#pragma unroll 1
+    for (int n = 0; n < H; ++n) {
+        if (PARAM != ZERO_ORDER) {
+            const int idx = kp.sp_index[n];
+            if (idx != cur) {
+                cur = idx;
+#pragma unroll
+                for (int l = 0; l < 4; ++l) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        if (PARAM == CUBIC) {                 // S:219-255
+                            const int s0 = 10 * idx + 4 * a;
+                            const float p0 = QP_KNOT(l, s0), p1 = QP_KNOT(l, s0 + 1), p2 = QP_KNOT(l, s0 + 2), p3 = QP_KNOT(l, s0 + 3);
+                            ka[l][a] = p1;
+                            kb[l][a] = 0.5f * ((p2 - p1) + (p1 - p0));
+                            kc[l][a] = p2;
+                            kd[l][a] = 0.5f * ((p3 - p2) + (p2 - p1));
+                        } else {                              // S:196-199
+                            const int s0 = idx + (kp.ns + 1) * a;
+                            ka[l][a] = QP_KNOT(l, s0);
+                            kb[l][a] = QP_KNOT(l, s0 + 1);
+                        }
+                    }
+                }
+            }
+        }
+        const float w0 = kp.basis[n][0], w1 = kp.basis[n][1], w2 = kp.basis[n][2], w3 = kp.basis[n][3];
+        const float fref = s_fref[n];
+        float Fx = 0.f, Fy = 0.f, Fz = 0.f, tx = 0.f, ty = 0.f, tz = 0.f;
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const float c = s_contact[l * H + n];
+            if (c != 0.0f) {
+                float fx, fy, fz;
+                if (PARAM == CUBIC) {
+                    fx = w0 * ka[l][0] + w1 * kb[l][0] + w2 * kc[l][0] + w3 * kd[l][0];
+                    fy = w0 * ka[l][1] + w1 * kb[l][1] + w2 * kc[l][1] + w3 * kd[l][1];
+                    fz = w0 * ka[l][2] + w1 * kb[l][2] + w2 * kc[l][2] + w3 * kd[l][2];
+                } else if (PARAM == LINEAR) {
+                    fx = w0 * ka[l][0] + w1 * kb[l][0];
+                    fy = w0 * ka[l][1] + w1 * kb[l][1];
+                    fz = w0 * ka[l][2] + w1 * kb[l][2];
+                } else {                                      // S:259-268
+                    fx = QP_KNOT(l, n); fy = QP_KNOT(l, n + H); fz = QP_KNOT(l, n + 2 * H);
+                }
+                fz = fref + fz;                               // S:382-385
+                fx = fx * third; fy = fy * third;             // S:388-402 with contact == 1
+                clamp_leg(kp, fx, fy, fz);                    // S:405-409
+                add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
+            }
+        }
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);   // S:446-451,491
+    }
+    return cost;
+}
+
+// Spline with a per-thread clock (adaptive rollouts and nothing else): S:181-268 with step = n_leg, A:353-374.
+template <int PARAM>
+__device__ __forceinline__ void spline_dyn(const KParams &kp, const float *s_best, const float *tcol, int l, int step,
+                                           float inv_denom, float &fx, float &fy, float &fz) {
+    const int PL = kp.P_leg;
+    if (PARAM == ZERO_ORDER) {
+        int j0 = step, j1 = step + kp.H, j2 = step + 2 * kp.H;    // int16(step); negative indices wrap like jnp
+        if (j0 < 0) j0 += PL;
+        if (j1 < 0) j1 += PL;
+        if (j2 < 0) j2 += PL;
+        fx = QP_KNOT(l, j0); fy = QP_KNOT(l, j1); fz = QP_KNOT(l, j2);
+        return;
+    }
+    const float stepf = (float)step;
+    int idx = 0;
+    for (int i = 1; i <= kp.ns; ++i) idx = (stepf >= kp.bounds[i]) ? i : idx;      // S:187-189
+    idx = idx < kp.ns ? idx : kp.ns - 1;                                           // unreachable guard (step < H)
+    const float q = fmaf(stepf, inv_denom, -(float)idx);                           // S:191-194
+    if (PARAM == LINEAR) {
+        const int sh = kp.ns + 1;
+        fx = (1.0f - q) * QP_KNOT(l, idx) + q * QP_KNOT(l, idx + 1);
+        fy = (1.0f - q) * QP_KNOT(l, idx + sh) + q * QP_KNOT(l, idx + sh + 1);
+        fz = (1.0f - q) * QP_KNOT(l, idx + 2 * sh) + q * QP_KNOT(l, idx + 2 * sh + 1);
+        return;
+    }
+    const float q2 = q * q, q3 = q2 * q;
+    const float a = 2.0f * q3 - 3.0f * q2 + 1.0f, bb = q3 - 2.0f * q2 + q, c = -2.0f * q3 + 3.0f * q2, d = q3 - q2;
+    const int s0 = 10 * idx;
+    float f[3];
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+        const float p0 = QP_KNOT(l, s0 + 4 * ax), p1 = QP_KNOT(l, s0 + 4 * ax + 1), p2 = QP_KNOT(l, s0 + 4 * ax + 2),
+                    p3 = QP_KNOT(l, s0 + 4 * ax + 3);
+        const float phi = 0.5f * ((p2 - p1) + (p1 - p0)), phin = 0.5f * ((p3 - p2) + (p2 - p1));
+        f[ax] = a * p1 + bb * phi + c * p2 + d * phin;
+    }
+    fx = f[0]; fy = f[1]; fz = f[2];
+}
+
+// Gait-adaptive rollout (A:326-501): per-sample contact sequence from the phase clock (G:68-89,136-151),
+// per-leg stance counters as spline clocks, plus the step-frequency cost A:500.
+template <int PARAM>
+__device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float *s_in, const float *tcol, float freq) {
+    const float *s_best = s_in + kp.off_best;
+    const float *ref = s_in + IN_REF;
+    const float *feet = s_in + IN_STATE + 12;
+    const int H = kp.H;
+    constexpr float third = 1.0f / 3.0f;
+    const float adv = kp.mpc_dt * freq;                       // G:79
+    float tt[4], inv_denom[4];
+    int nleg[4];
+    // pass 1: horizon_leg = sum_n contact + 1, A:345-348
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        float t = s_in[IN_PHASE + l];
+        float cnt = 0.0f;
+        for (int n = 0; n < H; ++n) {
+            t = t >= 1.0f ? 0.0f : t;                          // G:73-76
+            t = t + adv;                                       // G:79-82
+            cnt += (t < kp.duty) ? 1.0f : 0.0f;                // G:84-87
+        }
+        inv_denom[l] = 1.0f / ((cnt + 1.0f) * kp.inv_ns);      // 1 / (horizon_leg / num_spline), S:191
+        tt[l] = s_in[IN_PHASE + l];
+        nleg[l] = -1;                                          // A:339
+    }
+    Body b = load_body(s_in + IN_STATE);
+    float cost = 0.0f;
+#pragma unroll 1
+    for (int n = 0; n < H; ++n) {
+        float c[4];
+        float nst = 0.0f;
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            float t = tt[l];
+            t = t >= 1.0f ? 0.0f : t;
+            t = t + adv;
+            tt[l] = t;
+            c[l] = (t < kp.duty) ? 1.0f : 0.0f;
+            nleg[l] += (int)c[l];                              // A:353-356
+            nst += c[l];
+        }
+        const float fref = kp.mg / nst;                        // A (=S:377-380); inf when no leg is in stance
+        float Fx = 0.f, Fy = 0.f, Fz = 0.f, tx = 0.f, ty = 0.f, tz = 0.f;
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            if (c[l] != 0.0f) {                                // swing legs contribute exactly zero (see rollout_fixed)
+                float fx, fy, fz;
+                spline_dyn<PARAM>(kp, s_best, tcol, l, nleg[l], inv_denom[l], fx, fy, fz);
+                fz = fref + fz;
+                fx = fx * third; fy = fy * third;
+                clamp_leg(kp, fx, fy, fz);
+                add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
+            }
+        }
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);
+    }
+    const float df = freq - 1.3f;
+    cost += df * 100.0f * df;                                  // A:500
+    return cost;
+}
+
+// ======================================================================================================
+// block-level helpers
+// ======================================================================================================
+// lexicographic (cost, index) minimum over the block; result valid in every thread. s_red: >= 2*(TB/32) floats
+__device__ __forceinline__ void block_argmin(float &c, int &i, float *s_red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oc = __shfl_xor_sync(0xffffffffu, c, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (oc < c || (oc == c && oi < i)) { c = oc; i = oi; }
+    }
+    const int w = threadIdx.x >> 5, nw = TB / 32;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { s_red[w] = c; s_red[nw + w] = __int_as_float(i); }
+    __syncthreads();
+    c = s_red[0]; i = __float_as_int(s_red[nw]);
+#pragma unroll
+    for (int k = 1; k < nw; ++k) {
+        const float oc = s_red[k];
+        const int oi = __float_as_int(s_red[nw + k]);
+        if (oc < c || (oc == c && oi < i)) { c = oc; i = oi; }
+    }
+}
+
+// fixed-order block sum (deterministic); result valid in every thread
+__device__ __forceinline__ float block_sum(float v, float *s_red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, nw = TB / 32;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[w] = v;
+    __syncthreads();
+    float s = s_red[0];
+#pragma unroll
+    for (int k = 1; k < nw; ++k) s += s_red[k];
+    return s;
+}
+
+// Tail shared by the three control laws: GRF read-out at step 0 + one Euler step (S:695-784 = :839-928 = :985-1073).
+// spline(best_leg, 0.0, 1): zero-order -> p[0],p[H],p[2H]; linear -> p[0],p[ns+1],p[2(ns+1)]; cubic (q=0) -> p[1],p[5],p[9].
+// Executed by one thread.  best: P floats (shared or global).
+template <int PARAM>
+__device__ void tail_grf_pred(const KParams &kp, const float *s_in, const float *best, float *out) {
+    const float *s_contact = s_in + IN_CONTACT;
+    const int H = kp.H;
+    float c[4], nst;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) c[l] = s_contact[l * H];
+    nst = ((c[0] + c[1]) + c[2]) + c[3];                       // S:714-716
+    const float fref = kp.mg / nst;                            // S:717
+    Body b = load_body(s_in + IN_STATE);
+    float Fx = 0.f, Fy = 0.f, Fz = 0.f, tx = 0.f, ty = 0.f, tz = 0.f;
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        const float *p = best + l * kp.P_leg;
+        float fx, fy, fz;
+        if (PARAM == ZERO_ORDER) { fx = p[0]; fy = p[H]; fz = p[2 * H]; }
+        else if (PARAM == LINEAR) { fx = p[0]; fy = p[kp.ns + 1]; fz = p[2 * (kp.ns + 1)]; }
+        else { fx = p[1]; fy = p[5]; fz = p[9]; }
+        fz = fref + fz;                                        // S:719-722
+        fx = fx * c[l] / 3.0f; fy = fy * c[l] / 3.0f; fz = fz * c[l];   // S:724-738
+        clamp_leg(kp, fx, fy, fz);                             // S:741-745
+        out[OUT_GRF + 3 * l] = fx; out[OUT_GRF + 3 * l + 1] = fy; out[OUT_GRF + 3 * l + 2] = fz;
+        if (c[l] != 0.0f) {                                    // M:111-116,132-135 multiply by stance again
+            const float *foot = s_in + IN_STATE + 12 + 3 * l;
+            add_leg(kp, b, foot, fx * c[l], fy * c[l], fz * c[l], Fx, Fy, Fz, tx, ty, tz);
+        }
+    }
+    const float zero_ref[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    (void)srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[0], zero_ref);   // S:784
+    out[OUT_PRED + 0] = b.px; out[OUT_PRED + 1] = b.py; out[OUT_PRED + 2] = b.pz;
+    out[OUT_PRED + 3] = b.vx; out[OUT_PRED + 4] = b.vy; out[OUT_PRED + 5] = b.vz;
+    out[OUT_PRED + 6] = b.roll; out[OUT_PRED + 7] = b.pitch; out[OUT_PRED + 8] = b.yaw;
+    out[OUT_PRED + 9] = b.wx; out[OUT_PRED + 10] = b.wy; out[OUT_PRED + 11] = b.wz;
+    for (int k = 12; k < 24; ++k) out[OUT_PRED + k] = s_in[IN_STATE + k];  // M:174 feet unchanged
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Exact top-k by (cost, index) over `n` costs in global memory: 64-bit composite keys (cost bits << 32 | idx),
+// MSB-first 8-bit radix select with shared-memory histograms, then a bitonic sort of the k winners.
+// costs are >= 0 (sum of squares; NaN/Inf already saturated to 1e6), so their bit patterns order like the floats.
+// Result: s_keys[0..k) sorted ascending = argsort(costs, stable)[:k] (S:1075).  s_keys: >= MAX_ELITE u64,
+// s_hist: >= 256 u32.  Called by all TB threads of one block.
+// ------------------------------------------------------------------------------------------------------
+__device__ void block_topk(const float *costs, int n, int idx_base, int k, unsigned long long *s_keys, unsigned int *s_hist,
+                           unsigned int *s_misc) {
+    const int t = threadIdx.x;
+    unsigned long long prefix = 0ull;      // selected high bits so far
+    int need = k;                          // how many we still need among keys matching the prefix
+    int decided_bits = 0;
+    // After the passes: every key < prefix(threshold) is in, plus all keys == threshold path ... composite keys are
+    // unique, so after 8 passes exactly one key matches the full prefix and `need` == 1.
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = 56 - 8 * pass;
+        for (int b = t; b < 256; b += TB) s_hist[b] = 0u;
+        __syncthreads();
+        const unsigned long long mask = decided_bits == 0 ? 0ull : (~0ull << (64 - decided_bits));
+        for (int i = t; i < n; i += TB) {
+            const unsigned long long key = ((unsigned long long)__float_as_uint(__ldcg(costs + i)) << 32) | (unsigned int)(idx_base + i);
+            if ((key & mask) == prefix) atomicAdd(&s_hist[(unsigned int)(key >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (t == 0) {
+            unsigned int acc = 0u; int d = 0;
+            for (; d < 256; ++d) { if (acc + s_hist[d] >= (unsigned int)need) break; acc += s_hist[d]; }
+            s_misc[0] = (unsigned int)d; s_misc[1] = acc;
+        }
+        __syncthreads();
+        prefix |= ((unsigned long long)s_misc[0]) << shift;
+        need -= (int)s_misc[1];
+        decided_bits += 8;
+        __syncthreads();
+    }
+    // prefix is now the k-th smallest composite key; gather every key <= prefix (exactly k of them)
+    if (t == 0) s_misc[2] = 0u;
+    for (int i = t; i < MAX_ELITE; i += TB) s_keys[i] = ~0ull;
+    __syncthreads();
+    for (int i = t; i < n; i += TB) {
+        const unsigned long long key = ((unsigned long long)__float_as_uint(__ldcg(costs + i)) << 32) | (unsigned int)(idx_base + i);
+        if (key <= prefix) { const unsigned int slot = atomicAdd(&s_misc[2], 1u); if (slot < MAX_ELITE) s_keys[slot] = key; }
+    }
+    __syncthreads();
+    // bitonic sort of MAX_ELITE keys (padding = ~0)
+    for (int size = 2; size <= MAX_ELITE; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = t; i < MAX_ELITE / 2; i += TB) {
+                const int lo = 2 * i - (i & (stride - 1));
+                const int hi = lo + stride;
+                const bool up = ((lo & size) == 0);
+                const unsigned long long a = s_keys[lo], b = s_keys[hi];
+                if ((a > b) == up) { s_keys[lo] = b; s_keys[hi] = a; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+}  // namespace qp

@@ -1,0 +1,368 @@
+// qpmpc_tick.cuh -- the fused tick kernel and its merge / finish stages (see qpmpc_kernels.cuh for the math).
+#pragma once
+#include "qpmpc_kernels.cuh"
+#include <math_constants.h>
+
+namespace qp {
+
+constexpr int MAXV = 6;                 // P <= MAXV * TB knots
+constexpr int SCRATCH_KEYS = 2048;      // u64 keys for the cross-shard elite merge (world * elite_k <= 2048)
+constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogram + misc
+
+// shared-memory carve-up (float offsets); every region starts 16-byte aligned
+struct Smem {
+    float *in, *fref, *w, *v, *red, *tile;
+    int *idx;                               // MAX_ELITE elite indices (CEM refit)
+    __device__ Smem(float *base, const KParams &kp) {
+        in = base;
+        fref = in + kp.in_stride;
+        w = fref + MAX_H;
+        v = w + TB;
+        red = v + kp.P;
+        idx = reinterpret_cast<int *>(red + 16);
+        tile = red + 16 + MAX_ELITE;
+    }
+};
+__host__ __device__ inline size_t smem_floats(int in_stride, int P) {
+    const size_t tile = (size_t)P * TS > (size_t)SCRATCH_FLOATS ? (size_t)P * TS : (size_t)SCRATCH_FLOATS;
+    return (size_t)in_stride + MAX_H + TB + P + 16 + MAX_ELITE + tile + 4;
+}
+
+__device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Smem &s) {
+    const float *gin = kp.in + (size_t)r * kp.in_stride;
+    for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
+    __syncthreads();
+    if (threadIdx.x < kp.H) {       // gravity compensation per step, S:377-380
+        const float *c = s.in + IN_CONTACT;
+        const int n = threadIdx.x, H = kp.H;
+        const float nst = ((c[n] + c[H + n]) + c[2 * H + n]) + c[3 * H + n];
+        s.fref[n] = kp.mg / nst;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ bool lex_less(float c, int i, float oc, int oi) { return c < oc || (c == oc && i < oi); }
+
+// Online-softmax merge of `n` records (m, idx, s, V[P]) spaced `stride` floats apart in global memory.
+// Result: M, IDX (lexicographic min), S, and V in s.v (MPPI / CEM only).  All TB threads participate.
+template <int METHOD>
+__device__ void merge_records(const float *recs, int n, size_t stride, int P, const Smem &s, float &M, int &IDX, float &S) {
+    const int t = threadIdx.x;
+    float c = CUDART_INF_F;
+    int i = 0x7fffffff;
+    for (int b = t; b < n; b += TB) {
+        const float m = __ldcg(recs + b * stride + REC_M);
+        const int id = __float_as_int(__ldcg(recs + b * stride + REC_IDX));
+        if (lex_less(m, id, c, i)) { c = m; i = id; }
+    }
+    block_argmin(c, i, s.red);
+    M = c; IDX = i; S = 0.0f;
+    if (METHOD == RANDOM_SAMPLING) return;
+    float vacc[MAXV];
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) vacc[j] = 0.0f;
+    for (int base = 0; base < n; base += TB) {
+        const int b = base + t;
+        float sc = 0.0f, sv = 0.0f;
+        if (b < n) {
+            const float m = __ldcg(recs + b * stride + REC_M);
+            sc = (m == CUDART_INF_F) ? 0.0f : expf(-(m - M));
+            sv = __ldcg(recs + b * stride + REC_S) * sc;
+        }
+        __syncthreads();
+        s.w[t] = sc;
+        S += block_sum(sv, s.red);          // contains the barriers that publish s.w
+        const int cnt = (n - base) < TB ? (n - base) : TB;
+#pragma unroll
+        for (int j = 0; j < MAXV; ++j) {
+            const int p = t + j * TB;
+            if (p < P) {
+                float acc = vacc[j];
+                const float *col = recs + (size_t)base * stride + REC_V + p;
+#pragma unroll 4
+                for (int k = 0; k < cnt; ++k) acc = fmaf(s.w[k], __ldcg(col + k * stride), acc);
+                vacc[j] = acc;
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) { const int p = t + j * TB; if (p < P) s.v[p] = vacc[j]; }
+    __syncthreads();
+}
+
+// bitonic sort of n (power of two) u64 keys in shared memory, ascending
+__device__ void bitonic_sort_u64(unsigned long long *keys, int n) {
+    for (int size = 2; size <= n; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = threadIdx.x; i < n / 2; i += TB) {
+                const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
+                const bool up = ((lo & size) == 0);
+                const unsigned long long a = keys[lo], b = keys[hi];
+                if ((a > b) == up) { keys[lo] = b; keys[hi] = a; }
+            }
+            __syncthreads();
+        }
+}
+
+// Last block of a robot: merge the block records into this shard's record (+ local top-k for CEM).
+template <int METHOD>
+__device__ void shard_reduce(const KParams &kp, int r, const Smem &s) {
+    const int t = threadIdx.x;
+    float M, S; int IDX;
+    merge_records<METHOD>(kp.blk_recs + (size_t)r * kp.nblk * kp.blk_rec_stride, kp.nblk, kp.blk_rec_stride, kp.P, s, M, IDX, S);
+    float *rec = kp.shard_send + (size_t)r * kp.shard_rec_stride;
+    if (t == 0) { rec[REC_M] = M; rec[REC_IDX] = __int_as_float(IDX); rec[REC_S] = S; rec[REC_PAD] = 0.0f; }
+    if (METHOD != RANDOM_SAMPLING)
+        for (int p = t; p < kp.P; p += TB) rec[REC_V + p] = s.v[p];
+    if (METHOD == CEM_MPPI) {
+        unsigned long long *keys = reinterpret_cast<unsigned long long *>(s.tile);
+        unsigned int *hist = reinterpret_cast<unsigned int *>(s.tile + 2 * SCRATCH_KEYS);
+        unsigned int *misc = hist + 256;
+        const int k = kp.elite_k < kp.n_local ? kp.elite_k : kp.n_local;
+        block_topk(kp.costs + (size_t)r * kp.n_local, kp.n_local, kp.sample_base, k, keys, hist, misc);
+        for (int j = t; j < kp.elite_k; j += TB) {
+            const unsigned long long key = j < k ? keys[j] : ~0ull;
+            rec[REC_V + kp.P + 2 * j] = __uint_as_float((unsigned int)(key >> 32));
+            rec[REC_V + kp.P + 2 * j + 1] = __uint_as_float((unsigned int)(key & 0xffffffffu));
+        }
+        __syncthreads();
+    }
+}
+
+// Merge `world` shard records, apply the control law update, GRF/predicted-state tail, CEM sigma refit; write `out`.
+//   random_sampling S:690-692 | mppi S:823-836 | cem_mppi S:969-982,1075-1081 (A:1115-1121)
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__device__ void finish(const KParams &kp, int r, const Smem &s, const float *recs, int world, size_t rec_stride) {
+    const int t = threadIdx.x;
+    float M, S; int IDX;
+    merge_records<METHOD>(recs, world, rec_stride, kp.P, s, M, IDX, S);
+    float *out = kp.out + (size_t)r * kp.out_stride;
+    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
+    const float *s_best = s.in + kp.off_best;
+    const float *s_sigma = s.in + kp.off_sigma;
+    // ---- new best into s.v ----
+    if (METHOD == RANDOM_SAMPLING) {                       // best = params[best_index], S:692
+        if (kp.noise_mode == NOISE_INJECTED) {
+            const float *row = kp.noise + ((size_t)r * kp.N + IDX) * kp.P;
+            for (int p = t; p < kp.P; p += TB) s.v[p] = s_best[p] + __ldg(row + p);
+        } else {
+            for (int q = t; q < kp.P / 4; q += TB) {
+                const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, IDX, q, s_sigma);
+                s.v[4 * q] = s_best[4 * q] + e.x; s.v[4 * q + 1] = s_best[4 * q + 1] + e.y;
+                s.v[4 * q + 2] = s_best[4 * q + 2] + e.z; s.v[4 * q + 3] = s_best[4 * q + 3] + e.w;
+            }
+        }
+    } else {                                               // best += sum_i w_i eps_i, S:828-836
+        const float inv = 1.0f / S;
+        for (int p = t; p < kp.P; p += TB) s.v[p] = fmaf(s.v[p], inv, s_best[p]);
+    }
+    __syncthreads();
+    for (int p = t; p < kp.P; p += TB) {
+        out[OUT_BEST + p] = s.v[p];
+        if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + kp.off_best + p] = s.v[p];
+    }
+    if (t == 0) {
+        tail_grf_pred<PARAM>(kp, s.in, s.v, out);
+        out[OUT_BESTCOST] = M;
+        out[OUT_BESTIDX] = __int_as_float(IDX);
+        float bf;
+        if (ADAPTIVE) bf = sample_step_freq<METHOD>(kp, s.in, r, IDX);             // A:705,861,1022
+        else bf = (METHOD == CEM_MPPI) ? 1.65f : 1.4f;                               // S:786,930,1083
+        out[OUT_BESTFREQ] = bf;
+        if (METHOD != CEM_MPPI) out[OUT_NELITE] = __int_as_float(0);
+    }
+    if (METHOD != CEM_MPPI) return;
+    // ---- CEM elite refit ----
+    unsigned long long *keys = reinterpret_cast<unsigned long long *>(s.tile);
+    const int K = kp.elite_k;
+    const int total = world * K;
+    int npow = 2;
+    while (npow < total) npow <<= 1;
+    __syncthreads();
+    for (int j = t; j < npow; j += TB) {
+        unsigned long long key = ~0ull;
+        if (j < total) {
+            const int w = j / K, e = j - w * K;
+            const float *rec = recs + (size_t)w * rec_stride;
+            const unsigned int cb = __float_as_uint(__ldcg(rec + REC_V + kp.P + 2 * e));
+            const unsigned int ib = __float_as_uint(__ldcg(rec + REC_V + kp.P + 2 * e + 1));
+            key = ((unsigned long long)cb << 32) | ib;
+        }
+        keys[j] = key;
+    }
+    __syncthreads();
+    bitonic_sort_u64(keys, npow);
+    const int k = K < kp.N ? K : kp.N;                     // argsort(costs)[:k]
+    int *out_elite = reinterpret_cast<int *>(out + kp.off_out_elite);
+    for (int j = t; j < K; j += TB) {
+        const int id = j < k ? (int)(unsigned int)(keys[j] & 0xffffffffu) : -1;
+        out_elite[j] = id;
+        if (j < MAX_ELITE) s.idx[j] = id;
+    }
+    if (t == 0) out[OUT_NELITE] = __int_as_float(k);
+    __syncthreads();                                       // the tile scratch (keys) is reused for the elite rows below
+    // Per-knot mean / M2 over the elites, chunked by TB rows with an exact two-pass inside a chunk and Chan's
+    // pairwise update between chunks (same result as the two-pass diag(cov) of S:1077 to rounding).
+    float n_acc = 0.0f;
+    float mean_acc[MAXV], m2_acc[MAXV];
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) { mean_acc[j] = 0.0f; m2_acc[j] = 0.0f; }
+    for (int base = 0; base < k; base += TB) {
+        const int cnt = (k - base) < TB ? (k - base) : TB;
+        __syncthreads();
+        const int my_idx = (t < cnt) ? s.idx[base + t] : -1;
+        if (t < cnt) {
+            float *tcol = s.tile + t;
+            if (kp.noise_mode == NOISE_INJECTED) {
+                const float *row = kp.noise + ((size_t)r * kp.N + my_idx) * kp.P;
+                for (int p = 0; p < kp.P; ++p) tcol[p * TS] = __ldg(row + p);
+            } else {
+                for (int q = 0; q < kp.P / 4; ++q) {
+                    const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, my_idx, q, s_sigma);
+                    tcol[(4 * q) * TS] = e.x; tcol[(4 * q + 1) * TS] = e.y; tcol[(4 * q + 2) * TS] = e.z; tcol[(4 * q + 3) * TS] = e.w;
+                }
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < MAXV; ++j) {
+            const int p = t + j * TB;
+            if (p < kp.P) {
+                const float *rowp = s.tile + p * TS;
+                float sum = 0.0f;
+                for (int e = 0; e < cnt; ++e) sum += rowp[e];
+                const float mean_c = sum / (float)cnt;
+                float m2_c = 0.0f;
+                for (int e = 0; e < cnt; ++e) { const float d = rowp[e] - mean_c; m2_c = fmaf(d, d, m2_c); }
+                if (base == 0) { mean_acc[j] = mean_c; m2_acc[j] = m2_c; }
+                else {
+                    const float na = n_acc, nb = (float)cnt, nt = na + nb;
+                    const float delta = mean_c - mean_acc[j];
+                    mean_acc[j] = mean_acc[j] + delta * (nb / nt);
+                    m2_acc[j] = m2_acc[j] + m2_c + delta * delta * (na * nb / nt);
+                }
+            }
+        }
+        n_acc += (float)cnt;
+    }
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) {
+        const int p = t + j * TB;
+        if (p < kp.P) {
+            const float var = m2_acc[j] / (float)(k - 1) + 1e-8f;          // diag(cov(elite)) + 1e-8, S:1077-1078
+            float sg;
+            if (ADAPTIVE) { sg = var > 3.0f ? 3.0f : var; sg = sg < 0.5f ? 0.5f : sg; }      // A:1118-1121 (no sqrt)
+            else { sg = sqrtf(var); sg = sg > 5.0f ? 5.0f : sg; sg = sg < 0.2f ? 0.2f : sg; } // S:1079-1081
+            out[kp.off_out_sigma + p] = sg;
+        }
+    }
+}
+
+// ======================================================================================================
+// The tick kernel.  grid = (nblk, R), block = TB.  dynamic smem = smem_floats(...) * 4 bytes.
+// ======================================================================================================
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KParams kp) {
+    extern __shared__ __align__(16) float smem_raw[];
+    const Smem s(smem_raw, kp);
+    const int t = threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
+    __shared__ int s_last;
+    stage_inputs(kp, r, s);
+    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
+    const float *s_sigma = s.in + kp.off_sigma;
+    float *tcol = s.tile + t;
+    float m_run = CUDART_INF_F, s_run = 0.0f;
+    int idx_run = 0x7fffffff;
+    for (int p = t; p < kp.P; p += TB) s.v[p] = 0.0f;
+
+    for (int it = 0; it < kp.iters; ++it) {
+        const int tile_base = (blk * kp.iters + it) * TB;       // local (shard) index of this tile's first sample
+        if (tile_base >= kp.n_local) break;                     // block-uniform
+        const int local = tile_base + t;
+        const bool active = local < kp.n_local;
+        const int gi = kp.sample_base + local;                  // global sample index (row of the noise tensor)
+        // ---- 1. eps tile: tile[p][t] = additional_random_parameters[gi][p] ----
+        if (kp.noise_mode == NOISE_INJECTED) {
+            const int rows = (kp.n_local - tile_base) < TB ? (kp.n_local - tile_base) : TB;
+            const float *src = kp.noise + ((size_t)r * kp.N + kp.sample_base + tile_base) * kp.P;
+            for (int e = t; e < TB * kp.P; e += TB) {
+                const int row = e / kp.P, p = e - row * kp.P;
+                s.tile[p * TS + row] = row < rows ? __ldg(src + e) : 0.0f;
+            }
+            __syncthreads();
+        } else {
+            if (active) {
+                for (int q = 0; q < kp.P / 4; ++q) {
+                    const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, gi, q, s_sigma);
+                    tcol[(4 * q) * TS] = e.x; tcol[(4 * q + 1) * TS] = e.y; tcol[(4 * q + 2) * TS] = e.z; tcol[(4 * q + 3) * TS] = e.w;
+                }
+            } else {
+                for (int p = 0; p < kp.P; ++p) tcol[p * TS] = 0.0f;
+            }
+        }
+        // ---- 2. rollout + cost ----
+        float cost = CUDART_INF_F;
+        if (active) {
+            if (ADAPTIVE) {
+                const float freq = sample_step_freq<METHOD>(kp, s.in, r, gi);
+                cost = rollout_adaptive<PARAM>(kp, s.in, tcol, freq);
+            } else {
+                cost = rollout_fixed<PARAM>(kp, s.in, s.fref, tcol);
+            }
+            if (kp.mode == MODE_TICK) {                          // NaN / +-Inf -> 1e6, S:686-687
+                if (isnan(cost) || isinf(cost)) cost = 1000000.0f;
+            }
+            kp.costs[(size_t)r * kp.n_local + local] = cost;
+        }
+        if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }
+        // ---- 3. tile reduction folded into the block's running record ----
+        float cmin = cost;
+        int imin = active ? gi : 0x7fffffff;
+        block_argmin(cmin, imin, s.red);
+        if (METHOD != RANDOM_SAMPLING) {
+            const float m_new = fminf(m_run, cmin);              // cmin is finite: the tile has >= 1 active sample
+            const float scale_old = (m_run == CUDART_INF_F) ? 0.0f : expf(-(m_run - m_new));
+            const float w = active ? expf(-(cost - m_new)) : 0.0f;   // exp(-(c - beta)/T), T = 1, S:828-830
+            __syncthreads();
+            s.w[t] = w;
+            const float s_tile = block_sum(w, s.red);            // barriers inside publish s.w and the tile
+            s_run = fmaf(s_run, scale_old, s_tile);
+            for (int p = t; p < kp.P; p += TB) {
+                const float *rowp = s.tile + p * TS;
+                float acc = 0.0f;
+#pragma unroll 4
+                for (int e = 0; e < TB; ++e) {
+                    const float we = s.w[e];
+                    if (we != 0.0f) acc = fmaf(we, rowp[e], acc);
+                }
+                s.v[p] = fmaf(s.v[p], scale_old, acc);
+            }
+        }
+        if (lex_less(cmin, imin, m_run, idx_run)) { m_run = cmin; idx_run = imin; }   // running (min, argmin), S:690
+        __syncthreads();
+    }
+    if (kp.mode == MODE_ROLLOUT) return;
+    float *rec = kp.blk_recs + ((size_t)r * kp.nblk + blk) * kp.blk_rec_stride;
+    if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
+    if (METHOD != RANDOM_SAMPLING)
+        for (int p = t; p < kp.P; p += TB) rec[REC_V + p] = s.v[p];
+    __threadfence();
+    __syncthreads();
+    if (t == 0) {
+        const unsigned int ticket = atomicAdd(kp.counters + r, 1u);
+        s_last = (ticket == (unsigned int)(kp.nblk - 1));
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    shard_reduce<METHOD>(kp, r, s);
+    if (kp.fused_finish) {
+        __threadfence();
+        __syncthreads();
+        finish<PARAM, ADAPTIVE, METHOD>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0);
+    }
+    if (t == 0) kp.counters[r] = 0u;
+}
+
+}  // namespace qp

@@ -1,0 +1,77 @@
+"""Shared helpers for the parity tests: build matching oracle / product configs and seeded noise tensors."""
+import numpy as np
+
+from oracle.sampling_oracle import OracleConfig, SamplingOracle
+import quadruped_pympc_b200 as qp
+from quadruped_pympc_b200 import synthetic
+
+# Tolerances stated by BASELINE.json's north_star
+COST_RTOL = 1e-5      # sample costs
+KNOT_RTOL = 1e-4      # returned GRFs / knots (plus a small absolute floor for values that pass through zero)
+
+PARAMS = ['zero_order', 'linear_spline', 'cubic_spline']
+METHODS = ['random_sampling', 'mppi', 'cem_mppi']
+
+
+def make_pair(robot='go2', N=1000, **kw):
+    """(oracle, controller, oracle_cfg) for the same configuration."""
+    ocfg = OracleConfig.for_robot(robot, num_parallel_computations=N, **kw)
+    pcfg = qp.SamplerConfig.for_robot(robot, num_parallel_computations=N, **kw)
+    return SamplingOracle(ocfg), qp.Sampling_MPC(pcfg), ocfg
+
+
+def seeded_noise(oracle, seed, sigma=None):
+    """additional_random_parameters (N,P) from the frozen legacy numpy MT19937 stream, assembled per method
+    exactly as the reference does (row a9)."""
+    rng = np.random.RandomState(seed)
+    N, P = oracle.N, oracle.P
+    method = oracle.cfg.sampling_method
+    if method == 'random_sampling':
+        k = int(N / 3)
+        return oracle.assemble_noise_random_sampling(rng.randn(k, P), rng.rand(N - 1 - 2 * k, P))
+    if method == 'mppi':
+        return oracle.assemble_noise_gaussian(rng.randn(N - 1, P), np.float32(oracle.cfg.sigma_mppi))
+    sig = np.full(P, oracle.cfg.sigma_cem_mppi, np.float32) if sigma is None else sigma
+    return oracle.assemble_noise_gaussian(rng.randn(N - 1, P), sig)
+
+
+def seeded_freqs(oracle, seed, nominal=1.4, optimize_swing=1):
+    rng = np.random.RandomState(seed + 1000)
+    return oracle.assemble_step_frequencies(rng.randint(0, 3, oracle.N), nominal, optimize_swing)
+
+
+def run_both(oracle, ctrl, sc, best0, noise, sigma=None, freqs=None, optimize_swing=1):
+    """Tick the oracle and the CUDA controller on identical inputs; returns (oracle dict, product dict)."""
+    cem = oracle.cfg.sampling_method == 'cem_mppi'
+    adaptive = oracle.adaptive
+    ref = oracle.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, noise, sigma=sigma,
+                                 timing=sc['phase_signal'], nominal_step_frequency=sc['nominal_step_freq'],
+                                 optimize_swing=optimize_swing, step_frequencies=freqs)
+    key = ctrl.master_key
+    if cem:
+        args = (sigma, sc['phase_signal'], sc['nominal_step_freq'], optimize_swing)
+    else:
+        args = (sc['phase_signal'], sc['nominal_step_freq'], optimize_swing)
+    out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *args,
+                                      noise=noise, step_freqs=freqs if adaptive else None)
+    got = dict(nmpc_GRFs=out[0], nmpc_footholds=out[1], nmpc_predicted_state=out[2], best_control_parameters=out[3],
+               best_cost=out[4], best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
+    if cem:
+        got['new_sigma_cem_mppi'] = out[7]
+        got['elite_indices'] = ctrl.last_elite_indices
+    return ref, got
+
+
+def assert_tick_parity(ref, got, cem=False):
+    rel = np.max(np.abs(got['costs'] - ref['costs']) / np.maximum(np.abs(ref['costs']), 1e-12))
+    assert rel < COST_RTOL, f'cost rel err {rel:.3e} >= {COST_RTOL}'
+    assert got['best_index'] == ref['best_index'], (got['best_index'], ref['best_index'])
+    np.testing.assert_allclose(got['best_cost'], ref['best_cost'], rtol=COST_RTOL)
+    np.testing.assert_allclose(got['best_control_parameters'], ref['best_control_parameters'], rtol=KNOT_RTOL, atol=2e-4)
+    np.testing.assert_allclose(got['nmpc_GRFs'], ref['nmpc_GRFs'], rtol=KNOT_RTOL, atol=2e-4)
+    np.testing.assert_allclose(got['nmpc_predicted_state'], ref['nmpc_predicted_state'], rtol=KNOT_RTOL, atol=1e-6)
+    np.testing.assert_allclose(got['best_freq'], ref['best_freq'], rtol=1e-6)
+    if cem:
+        assert np.array_equal(got['elite_indices'], ref['elite_indices'])
+        np.testing.assert_allclose(got['new_sigma_cem_mppi'], ref['new_sigma_cem_mppi'], rtol=KNOT_RTOL, atol=1e-6)
+    return rel

@@ -1,0 +1,91 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the oracle on identical seeded inputs.
+
+Tolerances are BASELINE.json's: sample costs rel 1e-5; returned GRFs / knots rel 1e-4; argmin / elite indices exact.
+"""
+import numpy as np
+import pytest
+
+from quadruped_pympc_b200 import synthetic
+from helpers import (PARAMS, METHODS, make_pair, seeded_noise, seeded_freqs, run_both, assert_tick_parity,
+                     COST_RTOL)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('adaptive', [False, True])
+@pytest.mark.parametrize('method', METHODS)
+@pytest.mark.parametrize('param', PARAMS)
+def test_tick_parity_injected_noise(built, param, method, adaptive):
+    """3 parametrisations x 3 control laws x {fixed, adaptive}; N deliberately not a multiple of the tile (128)."""
+    N = 1337
+    oracle, ctrl, _ = make_pair('go2', N, control_parametrization=param, sampling_method=method,
+                                optimize_step_freq=adaptive)
+    for seed, gait in [(1, 'trot'), (7, 'pace')]:
+        sc = synthetic.scenario('go2', gait, seed=seed)
+        rng = np.random.RandomState(seed)
+        best0 = (0.5 * rng.randn(oracle.P)).astype(np.float32)
+        sigma = np.full(oracle.P, 3.0, np.float32) if method == 'cem_mppi' else None
+        noise = seeded_noise(oracle, seed, sigma)
+        freqs = seeded_freqs(oracle, seed) if adaptive else None
+        ref, got = run_both(oracle, ctrl, sc, best0, noise, sigma=sigma, freqs=freqs)
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
+
+
+@pytest.mark.parametrize('adaptive', [False, True])
+@pytest.mark.parametrize('param', PARAMS)
+def test_rollout_seam(built, param, adaptive):
+    """jit_vectorized_rollout (S:176-177 / A:186-187): explicit parameters in, raw costs out."""
+    N = 600
+    oracle, ctrl, _ = make_pair('aliengo', N, control_parametrization=param, optimize_step_freq=adaptive)
+    sc = synthetic.scenario('aliengo', 'trot', seed=11)
+    rng = np.random.RandomState(5)
+    params = (4.0 * rng.randn(N, oracle.P)).astype(np.float32)
+    if adaptive:
+        freqs = seeded_freqs(oracle, 3)
+        want = oracle.compute_rollout_adaptive(sc['state'], sc['reference'], sc['phase_signal'], params, freqs)
+        got = ctrl.jit_vectorized_rollout(sc['state'], sc['reference'], sc['phase_signal'], params, freqs)
+    else:
+        want = oracle.compute_rollout(sc['state'], sc['reference'], params, sc['contact_sequence'])
+        got = ctrl.jit_vectorized_rollout(sc['state'], sc['reference'], params, sc['contact_sequence'])
+    np.testing.assert_allclose(got, want, rtol=COST_RTOL)
+
+
+def test_config2_full_size(built):
+    """BASELINE config 2 at full size: Go2 trot, MPPI, cubic, N = 10,000 with injected noise."""
+    oracle, ctrl, _ = make_pair('go2', 10000, control_parametrization='cubic_spline', sampling_method='mppi')
+    sc = synthetic.scenario('go2', 'trot', seed=0)
+    best0 = np.zeros(oracle.P, np.float32)
+    noise = seeded_noise(oracle, 0)
+    ref, got = run_both(oracle, ctrl, sc, best0, noise)
+    assert_tick_parity(ref, got)
+
+
+def test_config1_full_size(built):
+    """BASELINE config 1: Aliengo trot, random_sampling, zero-order, N = 10,000."""
+    oracle, ctrl, _ = make_pair('aliengo', 10000, control_parametrization='zero_order', sampling_method='random_sampling')
+    sc = synthetic.scenario('aliengo', 'trot', seed=2)
+    best0 = np.zeros(oracle.P, np.float32)
+    noise = seeded_noise(oracle, 2)
+    ref, got = run_both(oracle, ctrl, sc, best0, noise)
+    assert_tick_parity(ref, got)
+
+
+def test_philox_tick_matches_oracle_on_exported_noise(built):
+    """Production mode (in-kernel Philox): the tick must equal the oracle fed with the noise the device exports."""
+    for method in METHODS:
+        oracle, ctrl, _ = make_pair('go2', 3000, control_parametrization='cubic_spline', sampling_method=method)
+        sc = synthetic.scenario('go2', 'trot', seed=4)
+        ctrl.with_newkey()
+        key = ctrl.master_key.copy()
+        sigma = np.linspace(0.5, 4.0, oracle.P).astype(np.float32) if method == 'cem_mppi' else None
+        noise = ctrl.generate_noise(key, sigma)
+        assert np.all(noise[0] == 0.0)
+        best0 = np.zeros(oracle.P, np.float32)
+        ref = oracle.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, noise, sigma=sigma)
+        args = (sigma,) if method == 'cem_mppi' else (sc['phase_signal'], sc['nominal_step_freq'], 0)
+        out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *args)
+        got = dict(nmpc_GRFs=out[0], nmpc_predicted_state=out[2], best_control_parameters=out[3], best_cost=out[4],
+                   best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
+        if method == 'cem_mppi':
+            got['new_sigma_cem_mppi'], got['elite_indices'] = out[7], ctrl.last_elite_indices
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
