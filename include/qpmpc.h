@@ -76,6 +76,7 @@ typedef struct qpmpc_config {
     float sigma_mppi;             /* config.py:192 */
     float step_freq_available[3]; /* config.py:109 */
     float pgg_duty_factor;        /* 0.65 hard-coded in A:179 */
+    int32_t robot_base;           /* global id of this handle's robot 0 (robot-partitioned multi-GPU runs; Philox key word 1) */
 } qpmpc_config;
 
 /* One robot's inputs for one tick = the arguments of jitted_compute_control (I:140-168) */
@@ -125,6 +126,15 @@ int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
 /* R robots in one launch (replaces "one process per robot", simulation/batched_simulations.py:43-58).
  * in / out are arrays of num_robots structs; parity hooks noise/step_freqs are honoured per robot. */
 int qpmpc_tick_batched(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
+/* The same for callers that keep the R robots in flat row-major arrays (states R x 24, references R x 24, contacts
+ * R x 4 x contact_ld, best / sigma R x P, phase_signals R x 4, per-robot nominal_step_freqs / optimize_swing; outputs
+ * grfs R x 12, predicted_states R x 24, best_out R x P, best_costs / best_freqs / best_indices R, sigma_new R x P).
+ * Optional pointers may be NULL.  One key (seed, counter) for the whole batch; robots differ in Philox key word 1. */
+int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, const float *references, const float *contacts,
+                            int32_t contact_ld, const float *best, const float *sigma, const float *phase_signals,
+                            const float *nominal_step_freqs, const int32_t *optimize_swing, const uint32_t key[2],
+                            float *grfs, float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
+                            int32_t *best_indices, float *sigma_new);
 /* costs (N) of the last tick of robot r, fetched lazily (the interface ignores them, I:138,158) */
 int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst);
 

@@ -39,6 +39,7 @@ class QpmpcConfig(C.Structure):
         ('inertia', C.c_float * 9), ('dts', C.c_float * MAX_HORIZON), ('mu', C.c_float), ('grf_min', C.c_float),
         ('grf_max', C.c_float), ('q_diag', C.c_float * 12), ('sigma_random_sampling', C.c_float * 3),
         ('sigma_mppi', C.c_float), ('step_freq_available', C.c_float * 3), ('pgg_duty_factor', C.c_float),
+        ('robot_base', C.c_int32),
     ]
 
 
@@ -65,6 +66,7 @@ class QpmpcTickOut(C.Structure):
 EXPORTS = [
     'qpmpc_abi_version', 'qpmpc_last_error', 'qpmpc_device_count', 'qpmpc_config_defaults', 'qpmpc_create',
     'qpmpc_destroy', 'qpmpc_num_parameters', 'qpmpc_num_local_samples', 'qpmpc_tick', 'qpmpc_tick_batched',
+    'qpmpc_tick_batched_flat',
     'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
@@ -114,6 +116,9 @@ def load():
     lib.qpmpc_num_local_samples.argtypes = [H]
     lib.qpmpc_tick.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
     lib.qpmpc_tick_batched.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
+    _IP, _UP = C.POINTER(C.c_int32), C.POINTER(C.c_uint32)
+    lib.qpmpc_tick_batched_flat.argtypes = [H, _FP, _FP, _FP, C.c_int32, _FP, _FP, _FP, _FP, _IP, _UP,
+                                            _FP, _FP, _FP, _FP, _FP, _IP, _FP]
     lib.qpmpc_get_costs.argtypes = [H, C.c_int, _FP]
     lib.qpmpc_rollout.argtypes = [H, _FP, _FP, _FP, C.c_int32, _FP, _FP, _FP, _FP]
     lib.qpmpc_generate_noise.argtypes = [H, C.c_int, C.POINTER(C.c_uint32), _FP, _FP]

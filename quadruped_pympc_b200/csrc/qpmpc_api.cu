@@ -168,6 +168,7 @@ static int validate_config(const qpmpc_config *c) {
     if (c->parametrization != QPMPC_ZERO_ORDER && (c->num_splines < 1 || c->num_splines > QPMPC_MAX_SPLINES))
         return fail(QPMPC_ERR_INVALID, "num_splines must be in [1,%d]", QPMPC_MAX_SPLINES);
     if (c->num_robots < 1) return fail(QPMPC_ERR_INVALID, "num_robots must be >= 1");
+    if (c->robot_base < 0) return fail(QPMPC_ERR_INVALID, "robot_base must be >= 0");
     if (c->shard_world < 1 || c->shard_rank < 0 || c->shard_rank >= c->shard_world) return fail(QPMPC_ERR_INVALID, "bad shard rank/world");
     if (!(c->mass > 0.f)) return fail(QPMPC_ERR_INVALID, "mass must be positive");
     if (c->elite_k < 0 || c->elite_k > QPMPC_MAX_ELITE) return fail(QPMPC_ERR_INVALID, "elite_k must be in [0,%d]", QPMPC_MAX_ELITE);
@@ -376,7 +377,7 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     rec[IN_OPTSWING] = u2f((uint32_t)in->optimize_swing);
     rec[IN_SEED] = u2f(in->key[0]);
     rec[IN_TICK] = u2f(in->key[1]);
-    rec[IN_ROBOT] = u2f((uint32_t)r);
+    rec[IN_ROBOT] = u2f((uint32_t)(h->cfg.robot_base + r));   // global robot id = Philox key word 1
     for (int l = 0; l < 4; ++l)
         for (int n = 0; n < h->H; ++n) {
             const float c = in->contact_sequence[(size_t)l * in->contact_ld + n];
@@ -498,6 +499,45 @@ extern "C" int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_o
     return run_tick(h, in, out);
 }
 extern "C" int qpmpc_tick_batched(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) { return run_tick(h, in, out); }
+
+// Structure-of-arrays form of qpmpc_tick_batched for host code that keeps R robots in flat arrays (one row per robot):
+// no per-robot struct marshalling.  sigma / phase_signal / nominal_step_freq / optimize_swing may be NULL when unused.
+extern "C" int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, const float *references, const float *contacts,
+                                       int32_t contact_ld, const float *best, const float *sigma, const float *phase_signals,
+                                       const float *nominal_step_freqs, const int32_t *optimize_swing, const uint32_t key[2],
+                                       float *grfs, float *predicted_states, float *best_out, float *best_costs,
+                                       float *best_freqs, int32_t *best_indices, float *sigma_new) {
+    if (!h || !states || !references || !contacts || !key) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    const int R = h->R, P = h->P;
+    std::vector<qpmpc_tick_in> in((size_t)R);
+    std::vector<qpmpc_tick_out> out((size_t)R);
+    for (int r = 0; r < R; ++r) {
+        qpmpc_tick_in &i = in[r];
+        memset(&i, 0, sizeof(i));
+        i.state = states + (size_t)r * 24; i.reference = references + (size_t)r * 24;
+        i.contact_sequence = contacts + (size_t)r * 4 * contact_ld; i.contact_ld = contact_ld;
+        i.best = best ? best + (size_t)r * P : nullptr;
+        i.sigma = sigma ? sigma + (size_t)r * P : nullptr;
+        i.phase_signal = phase_signals ? phase_signals + (size_t)r * 4 : nullptr;
+        i.nominal_step_freq = nominal_step_freqs ? nominal_step_freqs[r] : 0.f;
+        i.optimize_swing = optimize_swing ? optimize_swing[r] : 0;
+        i.key[0] = key[0]; i.key[1] = key[1];
+        qpmpc_tick_out &o = out[r];
+        memset(&o, 0, sizeof(o));
+        o.best = best_out ? best_out + (size_t)r * P : nullptr;
+        o.sigma_new = sigma_new ? sigma_new + (size_t)r * P : nullptr;
+    }
+    int rc = run_tick(h, in.data(), out.data());
+    if (rc) return rc;
+    for (int r = 0; r < R; ++r) {
+        if (grfs) memcpy(grfs + (size_t)r * 12, out[r].grfs, 12 * sizeof(float));
+        if (predicted_states) memcpy(predicted_states + (size_t)r * 24, out[r].predicted_state, 24 * sizeof(float));
+        if (best_costs) best_costs[r] = out[r].best_cost;
+        if (best_freqs) best_freqs[r] = out[r].best_freq;
+        if (best_indices) best_indices[r] = out[r].best_index;
+    }
+    return QPMPC_OK;
+}
 
 extern "C" int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst) {
     if (!h || !dst || robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "bad argument");
@@ -722,6 +762,7 @@ extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, fl
     if (flush_l2 && !h->d_flush) CK(cudaMalloc((void **)&h->d_flush, flush_bytes));
     KParams kp = h->kp;
     kp.in = h->d_in; kp.out = h->d_out;                      // inputs / outputs stay in HBM
+    kp.carry_best = 1;                                       // tick i+1 starts from tick i's best with the next Philox counter
     const dim3 grid(kp.nblk, h->R);
     for (int i = 0; i < steps; ++i) {
         if (flush_l2) CK(cudaMemsetAsync(h->d_flush, i & 0xff, flush_bytes, h->stream));

@@ -171,6 +171,8 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         else bf = (METHOD == CEM_MPPI) ? 1.65f : 1.4f;                               // S:786,930,1083
         out[OUT_BESTFREQ] = bf;
         if (METHOD != CEM_MPPI) out[OUT_NELITE] = __int_as_float(0);
+        // device-resident multi-tick runs: advance the Philox counter like with_newkey() does on the host (S:498-501)
+        if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + IN_TICK] = __uint_as_float(tick + 1u);
     }
     if (METHOD != CEM_MPPI) return;
     // ---- CEM elite refit ----
