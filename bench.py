@@ -47,6 +47,13 @@ FLOP_PER_TICK = N_SAMPLES * (HORIZON * FLOP_PER_ROLLOUT_STEP + P_KNOTS + 2 * P_K
 MULTI_ROBOTS_PER_GPU = 512
 
 
+def bench_config(robots, world):
+    return {'workload': workload_name(robots),
+            'parallelism': f'robots partitioned over {world} GPU(s), no collective',
+            'l2': 'flushed (256 MiB memset) before every timed tick, outside the events',
+            'noise': 'in-kernel Philox4x32-10 (GPU arm) / host Philox mirror (CPU arm)'}
+
+
 def workload_name(robots):
     return (f'{ROBOT} {GAIT}, {METHOD}, {PARAM} (P={P_KNOTS}), N={N_SAMPLES} samples, H={HORIZON}; '
             f'{robots} controller(s) per GPU')
@@ -97,3 +104,300 @@ class ClockSampler:
                     reasons.add(name)
         return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': smax, 'reasons': sorted(reasons),
                 'samples': len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# CPU arm: the C/OpenMP port of the reference tick (oracle/sampling_oracle.c), noise generation included
+# ----------------------------------------------------------------------------------------------------------------
+def cpu_tick_factory():
+    """Returns (tick(counter) -> best_cost, threads).  One call = one full reference tick on the host: draw the (N,P)
+    noise, perturb, N rollouts with cost, softmax-weighted update, GRF read-out (what jitted_compute_control does)."""
+    from oracle import c_oracle
+    from oracle.sampling_oracle import OracleConfig
+    from quadruped_pympc_b200 import synthetic
+    c_oracle.build()
+    ocfg = OracleConfig.for_robot(ROBOT, sampling_method=METHOD, control_parametrization=PARAM,
+                                  num_parallel_computations=N_SAMPLES)
+    orc = c_oracle.COracle(ocfg)
+    sc = synthetic.scenario(ROBOT, GAIT, seed=0)
+    state = {'best': np.zeros(orc.P, np.float32)}
+
+    def tick(counter):
+        noise = orc.noise(42, counter)
+        out = orc.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], state['best'], noise)
+        state['best'] = out['best_control_parameters']
+        return float(out['best_cost'])
+
+    return tick, c_oracle.num_threads()
+
+
+def time_cpu(seconds_budget, min_ticks=3, max_ticks=100000, warmup=2):
+    tick, threads = cpu_tick_factory()
+    for i in range(warmup):
+        tick(i)
+    t0 = time.perf_counter()
+    n = 0
+    while n < max_ticks and (n < min_ticks or time.perf_counter() - t0 < seconds_budget):
+        tick(warmup + n)
+        n += 1
+    dt = time.perf_counter() - t0
+    return {'value': n * N_SAMPLES * HORIZON / dt, 'unit': 'rollout-steps/s', 'cores': threads, 'kind': 'port',
+            'sample': f'{n} full ticks of the same workload (noise draw + {N_SAMPLES} rollouts x H={HORIZON} + MPPI update) '
+                      f'in {dt:.2f} s, C/OpenMP port of the reference tick (oracle/sampling_oracle.c), {threads} threads',
+            'ms_per_tick': 1e3 * dt / n}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path.  The reference's own JAX sampler cannot be
+    installed here (no jax/jaxlib wheel, no network), so this times the C/OpenMP port of its tick, all host threads."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    tick, threads = cpu_tick_factory()
+    for i in range(args.warmup):
+        tick(i)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        tick(args.warmup + i)
+    dt = time.perf_counter() - t0
+    value = args.steps * N_SAMPLES * HORIZON / dt
+    line = {'metric': 'rollout-steps/s', 'value': value, 'unit': 'rollout-steps/s', 'impl': 'reference',
+            'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': bench_config(1, args.gpus),
+            'cpu_baseline': {'value': value, 'unit': 'rollout-steps/s', 'cores': threads, 'kind': 'port',
+                             'sample': f'{args.steps} full ticks, C/OpenMP port of the reference tick '
+                                       f'(jax is not installable here), {threads} threads'},
+            'e2e': {'value': value, 'unit': 'rollout-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'tick_latency_us': {'p50': 1e6 * dt / args.steps}}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------------
+def _sampler_cfg(device):
+    import quadruped_pympc_b200 as qp
+    return qp.SamplerConfig.for_robot(ROBOT, sampling_method=METHOD, control_parametrization=PARAM,
+                                      num_parallel_computations=N_SAMPLES, device=device)
+
+
+def make_resident_handle(device, robots, robot_base):
+    """A handle with `robots` controllers whose tick packets are uploaded once and stay in HBM."""
+    from quadruped_pympc_b200 import _lib, synthetic
+    from quadruped_pympc_b200.sampling_mpc import make_c_config
+    lib = _lib.load()
+    c = make_c_config(_sampler_cfg(device), robots)
+    c.robot_base = robot_base
+    h = C.c_void_p()
+    _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
+    ins = (_lib.QpmpcTickIn * robots)()
+    keep = []
+    fp = lambda a: a.ctypes.data_as(_lib._FP)
+    for r in range(robots):
+        sc = synthetic.scenario(ROBOT, GAIT, seed=robot_base + r)
+        st, rf = sc['state'].astype(np.float32), sc['reference'].astype(np.float32)
+        cs = np.ascontiguousarray(sc['contact_sequence'], np.float32)
+        best = np.zeros(P_KNOTS, np.float32)
+        ph = sc['phase_signal'].astype(np.float32)
+        keep += [st, rf, cs, best, ph]
+        i = ins[r]
+        i.state, i.reference, i.contact_sequence, i.contact_ld, i.best = fp(st), fp(rf), fp(cs), cs.shape[1], fp(best)
+        i.phase_signal, i.nominal_step_freq, i.optimize_swing = fp(ph), float(sc['nominal_step_freq']), 0
+        i.key[0], i.key[1] = 42, 1
+    _lib.check(lib.qpmpc_upload_resident(h, ins))
+    return h, keep
+
+
+def run_resident(h, steps, warmup, flush=1):
+    """-> per-tick device times (ms) of `steps` resident ticks after `warmup` untimed ones, and the launch count."""
+    from quadruped_pympc_b200 import _lib
+    lib = _lib.load()
+    if warmup > 0:
+        w = np.zeros(warmup, np.float32)
+        _lib.check(lib.qpmpc_bench_resident(h, warmup, flush, w.ctypes.data_as(_lib._FP)))
+    n0, n1 = C.c_uint64(0), C.c_uint64(0)
+    _lib.check(lib.qpmpc_kernel_launch_count(h, C.byref(n0)))
+    ms = np.zeros(steps, np.float32)
+    _lib.check(lib.qpmpc_bench_resident(h, steps, flush, ms.ctypes.data_as(_lib._FP)))
+    _lib.check(lib.qpmpc_kernel_launch_count(h, C.byref(n1)))
+    return ms.astype(np.float64), int(n1.value - n0.value)
+
+
+def run_e2e(device, steps, warmup):
+    """The user-facing call with host buffers: Sampling_MPC.compute_control -> qpmpc_tick (H2D + kernel + D2H per tick).
+    -> (per-tick wall times in s, h2d bytes, d2h bytes, launches)"""
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200 import _lib, synthetic
+    ctrl = qp.Sampling_MPC(_sampler_cfg(device))
+    sc = synthetic.scenario(ROBOT, GAIT, seed=0)
+    best = np.zeros(P_KNOTS, np.float32)
+    lat = np.zeros(steps)
+    h = None
+    n0 = C.c_uint64(0)
+    for i in range(warmup + steps):
+        if i == warmup:
+            h = ctrl._ensure()
+            _lib.check(_lib.load().qpmpc_kernel_launch_count(h, C.byref(n0)))
+        ctrl.with_newkey()
+        t0 = time.perf_counter()
+        out = ctrl.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best, ctrl.master_key,
+                                   sc['phase_signal'], sc['nominal_step_freq'], 0)
+        t1 = time.perf_counter()
+        best = out[3]
+        if i >= warmup:
+            lat[i - warmup] = t1 - t0
+    n1 = C.c_uint64(0)
+    _lib.check(_lib.load().qpmpc_kernel_launch_count(h, C.byref(n1)))
+    in_floats = 60 + 4 * HORIZON + 2 * P_KNOTS          # tick packet: IN_CONTACT + 4H + best + sigma (include/qpmpc.h)
+    out_floats = 40 + 2 * P_KNOTS                       # GRF, predicted state, scalars, best, sigma_new
+    assert np.isfinite(float(out[4]))
+    return lat, 4 * ((in_floats + 3) // 4 * 4), 4 * ((out_floats + 3) // 4 * 4), int(n1.value - n0.value)
+
+
+def measure_fp32_peak(device):
+    from quadruped_pympc_b200 import _lib
+    tf = C.c_float(0)
+    _lib.check(_lib.load().qpmpc_measure_fp32_peak(device, C.byref(tf)))
+    return float(tf.value)
+
+
+def ncu_traffic_bytes():
+    """dram bytes per launch of the tick kernel from the committed `ncu --set full` capture (profiles/), or None."""
+    p = os.path.join(ROOT, 'profiles', 'tick_kernel_ncu_summary.json')
+    try:
+        with open(p) as f:
+            return json.load(f).get('dram_bytes_per_launch')
+    except (OSError, ValueError):
+        return None
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--robots', type=int, default=1, help='controllers per GPU in the headline measurement')
+    ap.add_argument('--multi-robots', type=int, default=MULTI_ROBOTS_PER_GPU)
+    ap.add_argument('--cpu-seconds', type=float, default=10.0)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == 'reference':
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: the sampling path has no CPU fallback '
+                         '(use --impl reference for the CPU arm)')
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200 import _lib
+    qp.build()
+    lib = _lib.load()
+    R = args.robots
+    fp32_peak = measure_fp32_peak(local)
+
+    # ---- headline: R controller(s) per GPU, resident in HBM ------------------------------------------------
+    h, keep = make_resident_handle(local, R, rank * R)
+    sampler = ClockSampler(local)
+    sampler.start()
+    run_resident(h, 1, args.warmup)                  # warm-up ticks (+1), untimed
+    barrier()
+    t0 = time.perf_counter()
+    ms, launches = run_resident(h, args.steps, 0)
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1)
+    total_ms = max_over_ranks(ms.sum())
+    units = world * R * N_SAMPLES * HORIZON * args.steps
+    value = units / (total_ms * 1e-3)
+    kernel_ms = float(ms.mean())
+    achieved_tf = R * FLOP_PER_TICK / (kernel_ms * 1e-3) / 1e12
+    hbm_bytes = R * (4 * (60 + 4 * HORIZON + 2 * P_KNOTS) + 4 * N_SAMPLES + 4 * (40 + 2 * P_KNOTS))
+    lib.qpmpc_destroy(h)
+
+    # ---- e2e through the public API with host buffers (rank-local controller; aggregate = world x) -----------
+    barrier()
+    lat, h2d, d2h, e2e_launches = run_e2e(local, args.steps, args.warmup)
+    barrier()
+    e2e_total = max_over_ranks(lat.sum())
+    e2e_value = world * N_SAMPLES * HORIZON * args.steps / e2e_total
+
+    # ---- multi-robot: `multi_robots` controllers per GPU in one batched launch ---------------------------------
+    MR = args.multi_robots
+    multi = None
+    if MR > 0:
+        hm, keepm = make_resident_handle(local, MR, rank * MR)
+        msteps = max(3, min(args.steps, 20))
+        run_resident(hm, 1, 3)
+        barrier()
+        mms, _ = run_resident(hm, msteps, 0)
+        barrier()
+        m_total = max_over_ranks(mms.sum())
+        m_tf = MR * FLOP_PER_TICK / (float(mms.mean()) * 1e-3) / 1e12
+        multi = {'robots_per_gpu': MR, 'robots': MR * world, 'steps': msteps,
+                 'ms_per_batched_tick': float(mms.mean()),
+                 'robot_ticks_per_s': world * MR * msteps / (m_total * 1e-3),
+                 'rollout_steps_per_s': world * MR * N_SAMPLES * HORIZON * msteps / (m_total * 1e-3),
+                 'roofline': {'bound': 'fp32', 'achieved': m_tf, 'peak': fp32_peak, 'unit': 'TFLOP/s',
+                              'frac': m_tf / fp32_peak}}
+        lib.qpmpc_destroy(hm)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = time_cpu(args.cpu_seconds)
+
+    if rank == 0:
+        line = {
+            'metric': 'rollout-steps/s', 'value': value, 'unit': 'rollout-steps/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total_ms / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': bench_config(R, world),
+            'tick_latency_us': {'device_p50': float(np.percentile(ms, 50) * 1e3), 'device_p99': float(np.percentile(ms, 99) * 1e3),
+                                'e2e_p50': float(np.percentile(lat, 50) * 1e6), 'e2e_p99': float(np.percentile(lat, 99) * 1e6)},
+            'e2e': {'value': e2e_value, 'unit': 'rollout-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                    'api': 'Sampling_MPC.compute_control -> qpmpc_tick (pinned H2D + kernel + D2H per tick)'},
+            'gpu_launches': launches + e2e_launches,
+            'roofline': {'bound': 'fp32', 'achieved': achieved_tf, 'peak': fp32_peak, 'unit': 'TFLOP/s',
+                         'frac': achieved_tf / fp32_peak, 'traffic': ncu_traffic_bytes(),
+                         'kernel': 'qp::tick_kernel<CUBIC,false,MPPI>', 'kernel_ms': kernel_ms,
+                         'algorithmic_flop_per_launch': R * FLOP_PER_TICK,
+                         'peak_source': 'FP32 FMA microbenchmark measured in this process (MEASURED_PEAKS.json has no '
+                                        'FP32 CUDA-core figure); latency-bound at 10k samples, see multi_robot.roofline',
+                         'hbm': {'algorithmic_bytes_per_launch': hbm_bytes,
+                                 'achieved_gbs': hbm_bytes / (kernel_ms * 1e-3) / 1e9}},
+            'clocks': clocks,
+        }
+        if multi:
+            line['multi_robot'] = multi
+        if cpu:
+            line['cpu_baseline'] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()
