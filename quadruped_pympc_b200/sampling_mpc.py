@@ -202,6 +202,47 @@ class Sampling_MPC:
         _lib.check(_lib.load().qpmpc_get_costs(self._ensure(), robot, _fp(out)))
         return out
 
+    # ------------------------------------------------------------------ sample-sharded controller
+    @staticmethod
+    def nccl_unique_id() -> bytes:
+        """128-byte ncclUniqueId made on one rank; broadcast it (e.g. `distributed.broadcast_bytes`) to the others."""
+        buf = (C.c_ubyte * 128)()
+        _lib.check(_lib.load().qpmpc_nccl_unique_id(_lib.find_libnccl().encode(), buf))
+        return bytes(buf)
+
+    def init_nccl(self, unique_id: bytes):
+        """Join the NCCL communicator of a sample-sharded controller (one rank per GPU, `shard_world` ranks)."""
+        if len(unique_id) != 128:
+            raise _lib.QpmpcError(_lib.ERR_INVALID, 'ncclUniqueId must be 128 bytes')
+        buf = (C.c_ubyte * 128).from_buffer_copy(unique_id)
+        _lib.check(_lib.load().qpmpc_shard_init_nccl(self._ensure(), _lib.find_libnccl().encode(), buf))
+        return self
+
+    def shard_partial(self, state, reference, contact_sequence, best, key, sigma=None, timing=None, nominal=None,
+                      optimize_swing=None, noise=None, step_freqs=None) -> np.ndarray:
+        """Rollouts + local reduction of this shard's slice; returns the shard record (floats) for a caller-side gather
+        (tests, or transports other than NCCL)."""
+        h, lib, b = self._ensure(), _lib.load(), self._buf
+        if self.sampling_method == 'cem_mppi':
+            sigma = np.broadcast_to(np.asarray(sigma, dtype=np.float32), (self.num_control_parameters,)).copy()
+        b.fill(state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing,
+               None if noise is None else _f32(noise), None if step_freqs is None else _f32(step_freqs), self.horizon)
+        self._tick_serial += 1
+        _lib.check(lib.qpmpc_shard_partial(h, C.byref(b.cin)))
+        rec = np.empty(lib.qpmpc_shard_record_floats(h), np.float32)
+        _lib.check(lib.qpmpc_shard_get_record(h, _fp(rec)))
+        return rec
+
+    def shard_finish(self, records):
+        """Merge the `shard_world` records (in rank order) and finish the tick; returns the usual tuple."""
+        h, lib, b = self._ensure(), _lib.load(), self._buf
+        if len(records) != self._shard[1]:
+            raise _lib.QpmpcError(_lib.ERR_INVALID, f'need {self._shard[1]} shard records, got {len(records)}')
+        for slot, rec in enumerate(records):
+            _lib.check(lib.qpmpc_shard_copy_record(h, slot, _fp(_f32(rec))))
+        _lib.check(lib.qpmpc_shard_finish(h, C.byref(b.cout)))
+        return self._unpack(b)
+
     # ------------------------------------------------------------------ reference surface (host side)
     def with_newkey(self):
         """S:498-501 (jax.random.split) -> advance the Philox counter."""

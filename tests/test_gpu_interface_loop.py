@@ -1,0 +1,79 @@
+"""GPU: the tick loop of SRBDControllerInterface.compute_control (I:118-176) replayed verbatim against the B200 class
+(dict inputs, prepare_state_and_reference, with_newkey / with_newsigma, several sampling iterations, several ticks with a
+lift-off in between) and against the oracle driven the same way on the noise the device exports."""
+import numpy as np
+import pytest
+
+import quadruped_pympc_b200 as qp
+from quadruped_pympc_b200 import synthetic
+from oracle.sampling_oracle import OracleConfig, SamplingOracle
+from helpers import COST_RTOL, KNOT_RTOL
+
+pytestmark = pytest.mark.gpu
+
+
+def _dicts(sc):
+    s, r = sc['state'], sc['reference']
+    st = dict(position=s[0:3], linear_velocity=s[3:6], orientation=s[6:9], angular_velocity=s[9:12],
+              foot_FL=s[12:15], foot_FR=s[15:18], foot_RL=s[18:21], foot_RR=s[21:24])
+    rf = dict(ref_position=r[0:3], ref_linear_velocity=r[3:6], ref_orientation=r[6:9], ref_angular_velocity=r[9:12],
+              ref_foot_FL=r[12:15].reshape(1, 3), ref_foot_FR=r[15:18].reshape(1, 3),
+              ref_foot_RL=r[18:21].reshape(1, 3), ref_foot_RR=r[21:24].reshape(1, 3))
+    return st, rf
+
+
+@pytest.mark.parametrize('method', ['random_sampling', 'mppi', 'cem_mppi'])
+def test_interface_tick_loop(built, method):
+    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=2000,
+              num_sampling_iterations=3)
+    controller = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
+    orc = SamplingOracle(OracleConfig.for_robot('go2', **kw))
+    best_ref = np.zeros(orc.P, np.float32)
+    previous_contact_mpc = np.array([1, 1, 1, 1])
+    sigma_cfg = 3                                              # cfg.mpc_params['sigma_cem_mppi']
+    for tick in range(4):
+        sc = synthetic.scenario('go2', 'trot', seed=10 + tick, sim_steps=60 * tick)
+        state_current, ref_state = _dicts(sc)
+        contact_sequence = np.concatenate([sc['contact_sequence'], np.ones((4, 12))], axis=1)   # (4, 2H) is allowed
+        current_contact = contact_sequence[:, 0].copy()
+        # ---- I:120-123
+        state_jax, ref_jax = controller.prepare_state_and_reference(state_current, ref_state, current_contact,
+                                                                    previous_contact_mpc)
+        s_o, r_o, best_ref = orc.prepare_state_and_reference(state_current, ref_state, current_contact,
+                                                            previous_contact_mpc, best_ref)
+        np.testing.assert_array_equal(state_jax, s_o)
+        np.testing.assert_array_equal(controller.best_control_parameters, best_ref)
+        previous_contact_mpc = current_contact
+        sigma_ref = None
+        for iter_sampling in range(controller.num_sampling_iterations):          # I:125
+            controller = controller.with_newkey()                                # I:126
+            if controller.sampling_method == 'cem_mppi':
+                if iter_sampling == 0:
+                    controller = controller.with_newsigma(sigma_cfg)             # I:128-129
+                    sigma_ref = np.full(orc.P, sigma_cfg, np.float32)
+                noise = controller.generate_noise(controller.master_key, controller.sigma_cem_mppi)
+                (nmpc_GRFs, nmpc_footholds, nmpc_predicted_state, controller.best_control_parameters, best_cost,
+                 best_sample_freq, costs, sigma_cem_mppi) = controller.jitted_compute_control(
+                    state_jax, ref_jax, contact_sequence, controller.best_control_parameters, controller.master_key,
+                    controller.sigma_cem_mppi)                                   # I:131-147
+                controller = controller.with_newsigma(sigma_cem_mppi)            # I:148
+            else:
+                noise = controller.generate_noise(controller.master_key)
+                (nmpc_GRFs, nmpc_footholds, nmpc_predicted_state, controller.best_control_parameters, best_cost,
+                 best_sample_freq, costs) = controller.jitted_compute_control(
+                    state_jax, ref_jax, contact_sequence, controller.best_control_parameters, controller.master_key,
+                    sc['phase_signal'], sc['nominal_step_freq'], 1)              # I:151-168
+            ref = orc.compute_control(s_o, r_o, contact_sequence[:, :12], best_ref, noise, sigma=sigma_ref)
+            rel = np.max(np.abs(np.asarray(costs) - ref['costs']) / np.abs(ref['costs']))
+            assert rel < COST_RTOL
+            assert controller.last_best_index == ref['best_index']
+            np.testing.assert_allclose(controller.best_control_parameters, ref['best_control_parameters'],
+                                       rtol=KNOT_RTOL, atol=2e-4)
+            np.testing.assert_allclose(np.array(nmpc_GRFs), ref['nmpc_GRFs'], rtol=KNOT_RTOL, atol=2e-4)
+            # carry the ORACLE's state forward from the device's best so that rounding does not accumulate across ticks
+            best_ref = np.asarray(controller.best_control_parameters, np.float32).copy()
+            if method == 'cem_mppi':
+                np.testing.assert_allclose(sigma_cem_mppi, ref['new_sigma_cem_mppi'], rtol=KNOT_RTOL, atol=1e-6)
+                sigma_ref = np.asarray(sigma_cem_mppi, np.float32).copy()
+        assert np.array(nmpc_GRFs).shape == (12,) and nmpc_footholds.shape == (12,)
+        assert np.all(np.array(nmpc_GRFs).reshape(4, 3)[current_contact == 0] == 0)

@@ -1,0 +1,66 @@
+"""GPU: one controller whose samples are split over `world` shards.  The shards are emulated on
+ONE GPU as `world` handles ticked one after another (no kernel waits on another, see B200_PROFILING.md); their records
+are gathered by the test instead of ncclAllGather, then every shard finishes.  Result must equal the unsharded tick and
+the oracle, with global argmin / elite indices."""
+import numpy as np
+import pytest
+
+import quadruped_pympc_b200 as qp
+from quadruped_pympc_b200 import synthetic
+from helpers import make_pair, seeded_noise, seeded_freqs, assert_tick_parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('world', [2, 3, 8])
+@pytest.mark.parametrize('method,adaptive', [('random_sampling', False), ('mppi', False), ('cem_mppi', False),
+                                             ('mppi', True), ('cem_mppi', True)])
+def test_sharded_tick_equals_oracle(built, method, adaptive, world):
+    N = 2501
+    oracle, _, _ = make_pair('go2', N, control_parametrization='cubic_spline', sampling_method=method,
+                             optimize_step_freq=adaptive)
+    sc = synthetic.scenario('go2', 'trot', seed=9)
+    rng = np.random.RandomState(3)
+    best0 = (0.5 * rng.randn(oracle.P)).astype(np.float32)
+    sigma = np.linspace(1.0, 4.0, oracle.P).astype(np.float32) if method == 'cem_mppi' else None
+    noise = seeded_noise(oracle, 5, sigma)
+    freqs = seeded_freqs(oracle, 5) if adaptive else None
+    ref = oracle.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, noise, sigma=sigma,
+                                 timing=sc['phase_signal'], nominal_step_frequency=sc['nominal_step_freq'],
+                                 optimize_swing=1, step_frequencies=freqs)
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=N, control_parametrization='cubic_spline',
+                                     sampling_method=method, optimize_step_freq=adaptive)
+    shards = [qp.Sampling_MPC(cfg, shard_rank=r, shard_world=world) for r in range(world)]
+    key = np.array([42, 1], np.uint32)
+    recs = [s.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sigma=sigma,
+                            timing=sc['phase_signal'], nominal=sc['nominal_step_freq'], optimize_swing=1,
+                            noise=noise, step_freqs=freqs) for s in shards]
+    outs = [s.shard_finish(recs) for s in shards]
+    costs = np.concatenate([np.asarray(o[6]) for o in outs])
+    for s, o in zip(shards, outs):
+        got = dict(nmpc_GRFs=o[0], nmpc_predicted_state=o[2], best_control_parameters=o[3], best_cost=o[4],
+                   best_freq=o[5], costs=costs, best_index=s.last_best_index)
+        if method == 'cem_mppi':
+            got['new_sigma_cem_mppi'], got['elite_indices'] = o[7], s.last_elite_indices
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
+    # every shard computed the identical result (deterministic merge in rank order)
+    for o in outs[1:]:
+        assert np.array_equal(o[3], outs[0][3]) and np.array_equal(o[0], outs[0][0])
+
+
+def test_sharded_philox_equals_unsharded(built):
+    """Production mode: shards draw their slice of the SAME global noise tensor (global row index in the counter)."""
+    N, world = 4000, 4
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=N, sampling_method='mppi')
+    sc = synthetic.scenario('go2', 'trot', seed=2)
+    key = np.array([42, 7], np.uint32)
+    best0 = np.zeros(96, np.float32)
+    whole = qp.Sampling_MPC(cfg).compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key,
+                                                 sc['phase_signal'], 1.4, 0)
+    shards = [qp.Sampling_MPC(cfg, shard_rank=r, shard_world=world) for r in range(world)]
+    recs = [s.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key) for s in shards]
+    out = shards[0].shard_finish(recs)
+    assert shards[0].last_best_index == int(np.argmin(np.asarray(whole[6])))
+    np.testing.assert_allclose(out[4], whole[4], rtol=1e-6)
+    np.testing.assert_allclose(out[3], whole[3], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(out[0], whole[0], rtol=1e-4, atol=1e-4)
