@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define QPMPC_ABI_VERSION 1
+#define QPMPC_ABI_VERSION 2
 #define QPMPC_MAX_HORIZON 64
 #define QPMPC_MAX_SPLINES 16
 #define QPMPC_MAX_ELITE 256
@@ -77,6 +77,8 @@ typedef struct qpmpc_config {
     float step_freq_available[3]; /* config.py:109 */
     float pgg_duty_factor;        /* 0.65 hard-coded in A:179 */
     int32_t robot_base;           /* global id of this handle's robot 0 (robot-partitioned multi-GPU runs; Philox key word 1) */
+    int32_t lanes_per_sample;     /* kernel variant: 1 = one sample per thread (throughput), 4 = four lanes per sample, one
+                                     leg each (latency: one controller at ~10k samples), 0 = choose by samples per launch */
 } qpmpc_config;
 
 /* One robot's inputs for one tick = the arguments of jitted_compute_control (I:140-168) */
@@ -172,6 +174,10 @@ int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in);
 int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms);
 int qpmpc_fetch_resident_out(qpmpc_handle *h, qpmpc_tick_out *out);  /* D2H of the last resident tick's outputs */
 int qpmpc_kernel_launch_count(const qpmpc_handle *h, uint64_t *count); /* kernels launched by this handle so far */
+/* Debug: runs ONE resident tick with %globaltimer stamps (ns) taken at phase boundaries.  out[0..5]: block 0 of robot 0
+ * (start, inputs staged, noise drawn, rollouts done, tile reduced, record published); out[8..11]: the last block of robot
+ * 0 (ticket taken, block records merged, -, result packet written).  Slots never reached stay 0. */
+int qpmpc_debug_phase_times(qpmpc_handle *h, uint64_t out[16]);
 /* FP32 FMA peak of the device (dependent-free FFMA streams on every SM), TFLOP/s; sm_mhz may be NULL */
 int qpmpc_measure_fp32_peak(int device, float *tflops);
 

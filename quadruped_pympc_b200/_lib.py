@@ -16,7 +16,7 @@ LIB_DIR = os.path.join(_HERE, 'lib')
 LIB_PATH = os.path.join(LIB_DIR, 'libqpmpc_b200.so')
 HEADER = os.path.join(ROOT, 'include', 'qpmpc.h')
 
-QPMPC_ABI_VERSION = 1
+QPMPC_ABI_VERSION = 2
 MAX_HORIZON, MAX_SPLINES, MAX_ELITE = 64, 16, 256
 PARAMETRIZATION = {'zero_order': 0, 'linear_spline': 1, 'cubic_spline': 2}
 METHOD = {'random_sampling': 0, 'mppi': 1, 'cem_mppi': 2}
@@ -39,7 +39,7 @@ class QpmpcConfig(C.Structure):
         ('inertia', C.c_float * 9), ('dts', C.c_float * MAX_HORIZON), ('mu', C.c_float), ('grf_min', C.c_float),
         ('grf_max', C.c_float), ('q_diag', C.c_float * 12), ('sigma_random_sampling', C.c_float * 3),
         ('sigma_mppi', C.c_float), ('step_freq_available', C.c_float * 3), ('pgg_duty_factor', C.c_float),
-        ('robot_base', C.c_int32),
+        ('robot_base', C.c_int32), ('lanes_per_sample', C.c_int32),
     ]
 
 
@@ -71,23 +71,40 @@ EXPORTS = [
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
     'qpmpc_tick_sharded', 'qpmpc_upload_resident', 'qpmpc_bench_resident', 'qpmpc_fetch_resident_out',
-    'qpmpc_kernel_launch_count', 'qpmpc_measure_fp32_peak',
+    'qpmpc_kernel_launch_count', 'qpmpc_measure_fp32_peak', 'qpmpc_debug_phase_times',
 ]
 
-NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-              '-Xcompiler', '-fPIC,-ffp-contract=off', '-shared']
+NVCC_COMPILE_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
+                      '-Xcompiler', '-fPIC,-ffp-contract=off', '-diag-suppress', '177,550']
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """nvcc-compile the CUDA library in-tree for sm_100a (cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))]
+    """nvcc-compile the CUDA library in-tree for sm_100a (cross-compiles without a GPU).  The translation units
+    (host API + six kernel-instantiation units) are compiled in parallel, then linked into one shared library."""
+    files = sorted(os.listdir(CSRC))
+    srcs = [os.path.join(CSRC, f) for f in files]
     newest = max(os.path.getmtime(p) for p in srcs + [HEADER])
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
-    cmd = ['nvcc'] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
-          [os.path.join(CSRC, 'qpmpc_api.cu'), '-o', LIB_PATH, '-ldl']
-    subprocess.check_call(cmd)
+    obj_dir = os.path.join(LIB_DIR, 'obj')
+    os.makedirs(obj_dir, exist_ok=True)
+    units = [f for f in files if f.endswith('.cu')]
+    procs = []
+    for u in units:
+        obj = os.path.join(obj_dir, u[:-3] + '.o')
+        cmd = ['nvcc'] + NVCC_COMPILE_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
+              ['-c', os.path.join(CSRC, u), '-o', obj]
+        procs.append((u, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    objs = []
+    for u, obj, p in procs:
+        out, _ = p.communicate()
+        if verbose or p.returncode != 0:
+            print(out)
+        if p.returncode != 0:
+            raise subprocess.CalledProcessError(p.returncode, f'nvcc -c {u}')
+        objs.append(obj)
+    subprocess.check_call(['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', LIB_PATH] + objs + ['-ldl'])
     return LIB_PATH
 
 
@@ -137,6 +154,7 @@ def load():
     lib.qpmpc_fetch_resident_out.argtypes = [H, C.POINTER(QpmpcTickOut)]
     lib.qpmpc_kernel_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
     lib.qpmpc_measure_fp32_peak.argtypes = [C.c_int, _FP]
+    lib.qpmpc_debug_phase_times.argtypes = [H, C.POINTER(C.c_uint64)]
     if lib.qpmpc_abi_version() != QPMPC_ABI_VERSION:
         raise QpmpcError(ERR_INVALID, 'libqpmpc_b200.so ABI version mismatch; rebuild')
     _lib = lib

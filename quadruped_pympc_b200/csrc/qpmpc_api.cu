@@ -1,7 +1,8 @@
 // qpmpc_api.cu -- host side of libqpmpc_b200.so: the C ABI declared in include/qpmpc.h.
 // No CPU fallback anywhere: every compute entry point needs a CUDA device and fails with QPMPC_ERR_CUDA otherwise.
 #include "../../include/qpmpc.h"
-#include "qpmpc_tick.cuh"
+#include "qpmpc_inst.cuh"
+#include "qpmpc_quad.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -13,6 +14,10 @@
 #include <vector>
 
 using namespace qp;
+
+// samples per launch (all robots) up to which the four-lanes-per-sample kernel is chosen automatically (measured
+// crossover on B200)
+static const long long QPMPC_QUAD_MAX_SAMPLES = 24576;
 
 // ------------------------------------------------------------------------------------------------------
 // error plumbing
@@ -36,16 +41,6 @@ static int fail(int code, const char *fmt, ...) {
 // ------------------------------------------------------------------------------------------------------
 // small kernels: finish stage of a sharded tick, noise / frequency export, FP32 peak probe
 // ------------------------------------------------------------------------------------------------------
-template <int PARAM, bool ADAPTIVE, int METHOD>
-__global__ void __launch_bounds__(TB, 4) finish_kernel(const __grid_constant__ KParams kp) {
-    extern __shared__ __align__(16) float smem_raw[];
-    const Smem s(smem_raw, kp);
-    const int r = blockIdx.y;
-    stage_inputs(kp, r, s);
-    finish<PARAM, ADAPTIVE, METHOD>(kp, r, s, kp.shard_recv + (size_t)r * kp.shard_rec_stride, kp.world,
-                                    (size_t)gridDim.y * kp.shard_rec_stride);
-}
-
 template <int METHOD>
 __global__ void noise_export_kernel(const __grid_constant__ KParams kp, uint32_t seed, uint32_t robot, uint32_t tick,
                                     const float *sigma, float *dst) {
@@ -80,13 +75,18 @@ __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
 // ------------------------------------------------------------------------------------------------------
 // kernel dispatch tables (parametrisation x adaptive x method)
 // ------------------------------------------------------------------------------------------------------
-typedef void (*KernelFn)(const KParams);
-#define QP_ROW(K, P, A) {K<P, A, RANDOM_SAMPLING>, K<P, A, MPPI>, K<P, A, CEM_MPPI>}
-#define QP_TABLE(K) {{QP_ROW(K, ZERO_ORDER, false), QP_ROW(K, ZERO_ORDER, true)},   \
-                     {QP_ROW(K, LINEAR, false), QP_ROW(K, LINEAR, true)},           \
-                     {QP_ROW(K, CUBIC, false), QP_ROW(K, CUBIC, true)}}
-static KernelFn g_tick_table[3][2][3] = QP_TABLE(tick_kernel);
-static KernelFn g_finish_table[3][2][3] = QP_TABLE(finish_kernel);
+static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3];
+static void fill_kernel_tables() {
+    static bool done = false;
+    if (done) return;
+    qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER]);
+    qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR]);
+    qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC]);
+    qp_inst_quad_zero(g_quad_table[ZERO_ORDER]);
+    qp_inst_quad_linear(g_quad_table[LINEAR]);
+    qp_inst_quad_cubic(g_quad_table[CUBIC]);
+    done = true;
+}
 
 // ------------------------------------------------------------------------------------------------------
 // NCCL through dlopen (no link-time dependency; the torch-bundled libnccl.so.2 is passed in by the host code)
@@ -124,7 +124,7 @@ struct qpmpc_handle {
     qpmpc_config cfg;
     KParams kp;                       // template: constants + device pointers for MODE_TICK
     int R, N, H, P, n_local;
-    size_t smem_bytes;
+    size_t smem_bytes, finish_smem_bytes;
     cudaStream_t stream = nullptr;
     float *d_in = nullptr, *d_out = nullptr, *d_costs = nullptr, *d_blk = nullptr, *d_send = nullptr, *d_recv = nullptr;
     float *d_noise = nullptr, *d_freqs = nullptr, *d_flush = nullptr, *d_sigma = nullptr;
@@ -138,6 +138,10 @@ struct qpmpc_handle {
     bool resident_uploaded = false, partial_done = false;
     NcclComm comm = nullptr;
     KernelFn tick_fn = nullptr, finish_fn = nullptr;
+    int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
+    int lanes = 1;                    // 1: sample per thread ; 4: four lanes per sample (qpmpc_quad.cuh)
+    unsigned long long *d_phase = nullptr;
+    KParams partial_kp;               // noise / frequency injection state carried from shard_partial to shard_finish
 };
 
 static size_t round4(size_t x) { return (x + 3) & ~(size_t)3; }
@@ -205,6 +209,7 @@ extern "C" void qpmpc_config_defaults(qpmpc_config *c) {
     c->sigma_mppi = 3.f;
     c->step_freq_available[0] = 1.4f; c->step_freq_available[1] = 2.0f; c->step_freq_available[2] = 2.4f;
     c->pgg_duty_factor = 0.65f;                                                   // A:179
+    c->robot_base = 0; c->lanes_per_sample = 0;
 }
 
 static void free_handle(qpmpc_handle *h) {
@@ -215,7 +220,7 @@ static void free_handle(qpmpc_handle *h) {
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     cudaFree(h->d_in); cudaFree(h->d_out); cudaFree(h->d_costs); cudaFree(h->d_blk); cudaFree(h->d_send); cudaFree(h->d_recv);
-    cudaFree(h->d_noise); cudaFree(h->d_freqs); cudaFree(h->d_flush); cudaFree(h->d_counters); cudaFree(h->d_sigma);
+    cudaFree(h->d_noise); cudaFree(h->d_freqs); cudaFree(h->d_flush); cudaFree(h->d_counters); cudaFree(h->d_sigma); cudaFree(h->d_phase);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->h_rec) cudaFreeHost(h->h_rec);
@@ -225,8 +230,9 @@ static void free_handle(qpmpc_handle *h) {
 
 extern "C" void qpmpc_destroy(qpmpc_handle *h) { free_handle(h); }
 
-static void plan_blocks(int n_local, int *iters, int *nblk) {
-    const int tiles = (n_local + TB - 1) / TB;
+static void plan_blocks(int n_local, int lanes, int *iters, int *nblk) {
+    const int per_tile = lanes == 4 ? QS : TB;         // samples per tile
+    const int tiles = (n_local + per_tile - 1) / per_tile;
     const int cap = 148 * 4 * 2;                       // two full waves of resident CTAs on 148 SMs
     int it = (tiles + cap - 1) / cap;
     if (it < 1) it = 1;
@@ -270,7 +276,12 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     memset(&kp, 0, sizeof(kp));
     kp.N = h->N; kp.n_local = h->n_local; kp.sample_base = base;
     kp.H = H; kp.ns = ns; kp.P = h->P; kp.P_leg = P_leg;
-    plan_blocks(h->n_local, &kp.iters, &kp.nblk);
+    // Kernel choice: the four-lanes-per-sample kernel wins while the GPU is under-filled (few samples in flight: one
+    // controller at 10k samples), the sample-per-thread kernel executes ~1.8x fewer instructions per sample and wins
+    // once its warps fill the machine.  lanes_per_sample = 0 picks by the number of samples of one launch.
+    if (cfg->lanes_per_sample != 0 && cfg->lanes_per_sample != 1 && cfg->lanes_per_sample != 4) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1 or 4"); }
+    h->lanes = cfg->lanes_per_sample ? cfg->lanes_per_sample : ((long long)h->n_local * h->R <= QPMPC_QUAD_MAX_SAMPLES ? 4 : 1);
+    plan_blocks(h->n_local, h->lanes, &kp.iters, &kp.nblk);
     kp.elite_k = elite_k;
     kp.mode = MODE_TICK; kp.noise_mode = NOISE_PHILOX; kp.freq_injected = 0;
     kp.fused_finish = (W == 1); kp.world = W; kp.carry_best = 0;
@@ -312,14 +323,20 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
             kp.basis[n][0] = 1.0f - q; kp.basis[n][1] = q;
         }
     }
-    h->smem_bytes = smem_floats(kp.in_stride, h->P) * sizeof(float);
+    h->threads = h->lanes == 4 ? QTB : TB;
+    h->finish_smem_bytes = smem_floats(kp.in_stride, h->P) * sizeof(float);
+    if (h->lanes == 4)      // the CEM elite refit of finish() stages up to `threads` noise rows in the tile
+        h->smem_bytes = smem_floats(kp.in_stride, h->P, QTB, cfg->method == QPMPC_CEM_MPPI ? QTB + 1 : QTS) * sizeof(float);
+    else
+        h->smem_bytes = h->finish_smem_bytes;
     if (h->smem_bytes > 227 * 1024) { delete h; return fail(QPMPC_ERR_INVALID, "tile of %d knots needs %zu B shared memory (> 227 KB)", h->P, h->smem_bytes); }
 
-    h->tick_fn = g_tick_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    fill_kernel_tables();
+    h->tick_fn = (h->lanes == 4 ? g_quad_table : g_tick_table)[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
-    CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
     CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
@@ -333,7 +350,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_in, R * kp.in_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_out, R * kp.out_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_costs, R * (size_t)h->N * sizeof(float)));
-    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + TB - 1) / TB)) * kp.blk_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + (h->lanes == 4 ? QS : TB) - 1) / (h->lanes == 4 ? QS : TB))) * kp.blk_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_send, R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_recv, (size_t)W * R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
@@ -425,7 +442,9 @@ static int ensure_freqs(qpmpc_handle *h, size_t floats) {
 
 static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid) {
     void *args[] = {(void *)&kp};
-    CK(cudaLaunchKernel((const void *)fn, grid, dim3(TB), args, h->smem_bytes, h->stream));
+    const bool is_finish = (fn == h->finish_fn);
+    CK(cudaLaunchKernel((const void *)fn, grid, dim3(is_finish ? TB : h->threads), args,
+                        is_finish ? h->finish_smem_bytes : h->smem_bytes, h->stream));
     h->launches++;
     return QPMPC_OK;
 }
@@ -475,7 +494,7 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
             CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, h->stream);
             void *args[] = {(void *)&kp};
-            cudaLaunchKernel((const void *)h->tick_fn, grid, dim3(TB), args, h->smem_bytes, h->stream);
+            cudaLaunchKernel((const void *)h->tick_fn, grid, dim3(h->threads), args, h->smem_bytes, h->stream);
             cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream);
             CK(cudaStreamEndCapture(h->stream, &g));
             CK(cudaGraphInstantiate(&h->graph_exec, g, 0));
@@ -562,7 +581,7 @@ extern "C" int qpmpc_rollout(qpmpc_handle *h, const float *state, const float *r
     if (rc) return rc;
     KParams kp = h->kp;
     kp.mode = MODE_ROLLOUT; kp.n_local = h->N; kp.sample_base = 0; kp.fused_finish = 0;
-    plan_blocks(h->N, &kp.iters, &kp.nblk);
+    plan_blocks(h->N, h->lanes, &kp.iters, &kp.nblk);
     const size_t per = (size_t)h->N * h->P;
     rc = ensure_noise(h, per);
     if (rc) return rc;
@@ -655,12 +674,10 @@ static int shard_finish_async(qpmpc_handle *h, const KParams &kp_in) {
     return QPMPC_OK;
 }
 
-static thread_local KParams g_partial_kp;   // noise/freq injection state carried from partial to finish
-
 extern "C" int qpmpc_shard_partial(qpmpc_handle *h, const qpmpc_tick_in *in) {
     if (!h || !in) return fail(QPMPC_ERR_INVALID, "NULL argument");
     CK(cudaSetDevice(h->cfg.device));
-    int rc = shard_partial_async(h, in, g_partial_kp);
+    int rc = shard_partial_async(h, in, h->partial_kp);
     if (rc) return rc;
     CK(cudaStreamSynchronize(h->stream));
     h->partial_done = true;
@@ -693,7 +710,7 @@ extern "C" int qpmpc_shard_finish(qpmpc_handle *h, qpmpc_tick_out *out) {
     if (!h || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
     if (!h->partial_done) return fail(QPMPC_ERR_STATE, "qpmpc_shard_finish without a preceding qpmpc_shard_partial");
     CK(cudaSetDevice(h->cfg.device));
-    int rc = shard_finish_async(h, g_partial_kp);
+    int rc = shard_finish_async(h, h->partial_kp);
     if (rc) return rc;
     CK(cudaStreamSynchronize(h->stream));
     for (int r = 0; r < h->R; ++r) unpack_one(h, r, h->h_out, &out[r]);
@@ -782,6 +799,22 @@ extern "C" int qpmpc_fetch_resident_out(qpmpc_handle *h, qpmpc_tick_out *out) {
     std::vector<float> tmp((size_t)h->R * h->kp.out_stride);
     CK(cudaMemcpy(tmp.data(), h->d_out, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
     for (int r = 0; r < h->R; ++r) unpack_one(h, r, tmp.data(), &out[r]);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_debug_phase_times(qpmpc_handle *h, uint64_t out[16]) {
+    if (!h || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h->resident_uploaded) return fail(QPMPC_ERR_STATE, "qpmpc_upload_resident has not been called");
+    if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "needs an unsharded handle");
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 16 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(h->d_phase, 0, 16 * sizeof(unsigned long long), h->stream));
+    KParams kp = h->kp;
+    kp.in = h->d_in; kp.out = h->d_out; kp.carry_best = 1; kp.phase_ns = h->d_phase;
+    int rc = launch(h, h->tick_fn, kp, dim3(kp.nblk, h->R));
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out, h->d_phase, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     return QPMPC_OK;
 }
 

@@ -71,7 +71,18 @@ struct KParams {
     unsigned int *counters;                 // [R]
     const float *noise;                     // injected: [R][N][P] (additional noise, or explicit params in MODE_ROLLOUT)
     const float *freqs;                     // injected: [R][N]
+    unsigned long long *phase_ns;           // debug (qpmpc_debug_phase_times): %globaltimer at phase boundaries, or NULL
 };
+
+// phase slots: block 0 of robot 0 -> [0..5] = start, staged, noise done, rollout done, tile reduced, record written ;
+//              the last block of robot 0 -> [8..11] = ticket taken, blocks merged, finish done (best), tail written
+__device__ __forceinline__ void phase_mark(const KParams &kp, int slot) {
+    if (kp.phase_ns != nullptr && threadIdx.x == 0 && blockIdx.y == 0) {
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        kp.phase_ns[slot] = ns;
+    }
+}
 
 // ======================================================================================================
 // RNG: Philox4x32-10, counter = (quad, row, tick, stream), key = (seed, robot)   (host mirror: oracle/sampling_oracle.c)
@@ -449,7 +460,9 @@ __device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float
 // block-level helpers
 // ======================================================================================================
 // lexicographic (cost, index) minimum over the block; result valid in every thread. s_red: >= 2*(TB/32) floats
+template <int NT>
 __device__ __forceinline__ void block_argmin(float &c, int &i, float *s_red) {
+    constexpr int TB = NT;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float oc = __shfl_xor_sync(0xffffffffu, c, o);
@@ -470,7 +483,9 @@ __device__ __forceinline__ void block_argmin(float &c, int &i, float *s_red) {
 }
 
 // fixed-order block sum (deterministic); result valid in every thread
+template <int NT>
 __device__ __forceinline__ float block_sum(float v, float *s_red) {
+    constexpr int TB = NT;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     const int w = threadIdx.x >> 5, nw = TB / 32;
@@ -529,8 +544,10 @@ __device__ void tail_grf_pred(const KParams &kp, const float *s_in, const float 
 // Result: s_keys[0..k) sorted ascending = argsort(costs, stable)[:k] (S:1075).  s_keys: >= MAX_ELITE u64,
 // s_hist: >= 256 u32.  Called by all TB threads of one block.
 // ------------------------------------------------------------------------------------------------------
-__device__ void block_topk(const float *costs, int n, int idx_base, int k, unsigned long long *s_keys, unsigned int *s_hist,
+template <int NT>
+static __device__ void block_topk(const float *costs, int n, int idx_base, int k, unsigned long long *s_keys, unsigned int *s_hist,
                            unsigned int *s_misc) {
+    constexpr int TB = NT;
     const int t = threadIdx.x;
     unsigned long long prefix = 0ull;      // selected high bits so far
     int need = k;                          // how many we still need among keys matching the prefix

@@ -13,22 +13,26 @@ constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogra
 struct Smem {
     float *in, *fref, *w, *v, *red, *tile;
     int *idx;                               // MAX_ELITE elite indices (CEM refit)
-    __device__ Smem(float *base, const KParams &kp) {
+    __device__ Smem(float *base, const KParams &kp, int nt = TB) {
         in = base;
         fref = in + kp.in_stride;
         w = fref + MAX_H;
-        v = w + TB;
+        v = w + nt;
         red = v + kp.P;
         idx = reinterpret_cast<int *>(red + 16);
         tile = red + 16 + MAX_ELITE;
     }
 };
-__host__ __device__ inline size_t smem_floats(int in_stride, int P) {
-    const size_t tile = (size_t)P * TS > (size_t)SCRATCH_FLOATS ? (size_t)P * TS : (size_t)SCRATCH_FLOATS;
-    return (size_t)in_stride + MAX_H + TB + P + 16 + MAX_ELITE + tile + 4;
+// nt: threads per block; tile_cols: tile row stride the kernel needs (nt + 1 for the sample-per-thread kernel and for
+// the CEM elite refit, nt / 4 + 1 for the four-lanes-per-sample kernel without CEM)
+__host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB, int tile_cols = TS) {
+    const size_t tile = (size_t)P * tile_cols > (size_t)SCRATCH_FLOATS ? (size_t)P * tile_cols : (size_t)SCRATCH_FLOATS;
+    return (size_t)in_stride + MAX_H + nt + P + 16 + MAX_ELITE + tile + 4;
 }
 
+template <int NT>
 __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Smem &s) {
+    constexpr int TB = NT;
     const float *gin = kp.in + (size_t)r * kp.in_stride;
     for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
     __syncthreads();
@@ -45,19 +49,81 @@ __device__ __forceinline__ bool lex_less(float c, int i, float oc, int oi) { ret
 
 // Online-softmax merge of `n` records (m, idx, s, V[P]) spaced `stride` floats apart in global memory.
 // Result: M, IDX (lexicographic min), S, and V in s.v (MPPI / CEM only).  All TB threads participate.
-template <int METHOD>
-__device__ void merge_records(const float *recs, int n, size_t stride, int P, const Smem &s, float &M, int &IDX, float &S) {
+template <int METHOD, int NT>
+__device__ void merge_records(const float *recs, int n, size_t stride, int P, const Smem &s, float &M, int &IDX, float &S,
+                              const KParams *dbg = nullptr) {
+    constexpr int TB = NT;
     const int t = threadIdx.x;
     float c = CUDART_INF_F;
     int i = 0x7fffffff;
     for (int b = t; b < n; b += TB) {
-        const float m = __ldcg(recs + b * stride + REC_M);
-        const int id = __float_as_int(__ldcg(recs + b * stride + REC_IDX));
+        const float m = recs[b * stride + REC_M];
+        const int id = __float_as_int(recs[b * stride + REC_IDX]);
         if (lex_less(m, id, c, i)) { c = m; i = id; }
     }
-    block_argmin(c, i, s.red);
+    block_argmin<TB>(c, i, s.red);
     M = c; IDX = i; S = 0.0f;
+    if (dbg) phase_mark(*dbg, 12);
     if (METHOD == RANDOM_SAMPLING) return;
+    // Fast path (P % 4 == 0, P/4 <= TB: every default configuration): float4 loads of the V rows, the records split
+    // over G = TB / (P/4) thread groups (independent coalesced loads in flight instead of one serial chain per knot),
+    // group partials combined in a fixed order -> deterministic.
+    const int nc = P >> 2;
+    if ((P & 3) == 0 && nc <= TB && (stride & 3) == 0) {
+        const int G = TB / nc;
+        const int g = t / nc, c4 = t - g * nc;
+        const size_t stride4 = stride >> 2;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int base = 0; base < n; base += TB) {
+            const int b = base + t;
+            float sc = 0.0f, sv = 0.0f;
+            if (b < n) {
+                const float m = recs[b * stride + REC_M];
+                sc = (m == CUDART_INF_F) ? 0.0f : expf(-(m - M));
+                sv = recs[b * stride + REC_S] * sc;
+            }
+            __syncthreads();
+            s.w[t] = sc;
+            S += block_sum<TB>(sv, s.red);          // contains the barriers that publish s.w
+            if (dbg && base == 0) phase_mark(*dbg, 13);
+            const int cnt = (n - base) < TB ? (n - base) : TB;
+            if (g < G) {
+                const float4 *col = reinterpret_cast<const float4 *>(recs + (size_t)base * stride + REC_V) + c4;
+                // eight independent 16-byte loads in flight per thread, then the FMAs in record order
+                for (int k0 = g; k0 < cnt; k0 += 8 * G) {
+                    float4 v[8];
+                    float w[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int k = k0 + u * G;
+                        const bool ok = k < cnt;
+                        v[u] = ok ? col[(size_t)k * stride4] : make_float4(0.f, 0.f, 0.f, 0.f);
+                        w[u] = ok ? s.w[k] : 0.0f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        acc.x = fmaf(w[u], v[u].x, acc.x); acc.y = fmaf(w[u], v[u].y, acc.y);
+                        acc.z = fmaf(w[u], v[u].z, acc.z); acc.w = fmaf(w[u], v[u].w, acc.w);
+                    }
+                }
+            }
+        }
+        if (dbg) phase_mark(*dbg, 14);
+        __syncthreads();
+        float4 *part = reinterpret_cast<float4 *>(s.tile);      // [G][nc] scratch (the tile is free at merge time)
+        if (g < G) part[g * nc + c4] = acc;
+        __syncthreads();
+        if (t < nc) {
+            float4 a = part[t];
+            for (int gg = 1; gg < G; ++gg) {
+                const float4 o = part[gg * nc + t];
+                a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
+            }
+            s.v[4 * t] = a.x; s.v[4 * t + 1] = a.y; s.v[4 * t + 2] = a.z; s.v[4 * t + 3] = a.w;
+        }
+        __syncthreads();
+        return;
+    }
     float vacc[MAXV];
 #pragma unroll
     for (int j = 0; j < MAXV; ++j) vacc[j] = 0.0f;
@@ -71,7 +137,7 @@ __device__ void merge_records(const float *recs, int n, size_t stride, int P, co
         }
         __syncthreads();
         s.w[t] = sc;
-        S += block_sum(sv, s.red);          // contains the barriers that publish s.w
+        S += block_sum<TB>(sv, s.red);          // contains the barriers that publish s.w
         const int cnt = (n - base) < TB ? (n - base) : TB;
 #pragma unroll
         for (int j = 0; j < MAXV; ++j) {
@@ -92,7 +158,9 @@ __device__ void merge_records(const float *recs, int n, size_t stride, int P, co
 }
 
 // bitonic sort of n (power of two) u64 keys in shared memory, ascending
-__device__ void bitonic_sort_u64(unsigned long long *keys, int n) {
+template <int NT>
+static __device__ void bitonic_sort_u64(unsigned long long *keys, int n) {
+    constexpr int TB = NT;
     for (int size = 2; size <= n; size <<= 1)
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
             for (int i = threadIdx.x; i < n / 2; i += TB) {
@@ -106,11 +174,11 @@ __device__ void bitonic_sort_u64(unsigned long long *keys, int n) {
 }
 
 // Last block of a robot: merge the block records into this shard's record (+ local top-k for CEM).
-template <int METHOD>
-__device__ void shard_reduce(const KParams &kp, int r, const Smem &s) {
+template <int METHOD, int NT>
+__device__ void shard_reduce(const KParams &kp, int r, const Smem &s, float &M, int &IDX, float &S) {
+    constexpr int TB = NT;
     const int t = threadIdx.x;
-    float M, S; int IDX;
-    merge_records<METHOD>(kp.blk_recs + (size_t)r * kp.nblk * kp.blk_rec_stride, kp.nblk, kp.blk_rec_stride, kp.P, s, M, IDX, S);
+    merge_records<METHOD, NT>(kp.blk_recs + (size_t)r * kp.nblk * kp.blk_rec_stride, kp.nblk, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
     float *rec = kp.shard_send + (size_t)r * kp.shard_rec_stride;
     if (t == 0) { rec[REC_M] = M; rec[REC_IDX] = __int_as_float(IDX); rec[REC_S] = S; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
@@ -120,7 +188,7 @@ __device__ void shard_reduce(const KParams &kp, int r, const Smem &s) {
         unsigned int *hist = reinterpret_cast<unsigned int *>(s.tile + 2 * SCRATCH_KEYS);
         unsigned int *misc = hist + 256;
         const int k = kp.elite_k < kp.n_local ? kp.elite_k : kp.n_local;
-        block_topk(kp.costs + (size_t)r * kp.n_local, kp.n_local, kp.sample_base, k, keys, hist, misc);
+        block_topk<NT>(kp.costs + (size_t)r * kp.n_local, kp.n_local, kp.sample_base, k, keys, hist, misc);
         for (int j = t; j < kp.elite_k; j += TB) {
             const unsigned long long key = j < k ? keys[j] : ~0ull;
             rec[REC_V + kp.P + 2 * j] = __uint_as_float((unsigned int)(key >> 32));
@@ -132,11 +200,14 @@ __device__ void shard_reduce(const KParams &kp, int r, const Smem &s) {
 
 // Merge `world` shard records, apply the control law update, GRF/predicted-state tail, CEM sigma refit; write `out`.
 //   random_sampling S:690-692 | mppi S:823-836 | cem_mppi S:969-982,1075-1081 (A:1115-1121)
-template <int PARAM, bool ADAPTIVE, int METHOD>
-__device__ void finish(const KParams &kp, int r, const Smem &s, const float *recs, int world, size_t rec_stride) {
+template <int PARAM, bool ADAPTIVE, int METHOD, int NT>
+__device__ void finish(const KParams &kp, int r, const Smem &s, const float *recs, int world, size_t rec_stride,
+                       bool premerged = false, float M = 0.0f, int IDX = 0, float S = 0.0f) {
+    constexpr int TB = NT;
+    constexpr int TS = NT + 1;
     const int t = threadIdx.x;
-    float M, S; int IDX;
-    merge_records<METHOD>(recs, world, rec_stride, kp.P, s, M, IDX, S);
+    // premerged: the caller (fused single-shard tick) has just produced (M, IDX, S, s.v) in shard_reduce
+    if (!premerged) merge_records<METHOD, NT>(recs, world, rec_stride, kp.P, s, M, IDX, S);
     float *out = kp.out + (size_t)r * kp.out_stride;
     const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
     const float *s_best = s.in + kp.off_best;
@@ -158,6 +229,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         for (int p = t; p < kp.P; p += TB) s.v[p] = fmaf(s.v[p], inv, s_best[p]);
     }
     __syncthreads();
+    phase_mark(kp, 10);
     for (int p = t; p < kp.P; p += TB) {
         out[OUT_BEST + p] = s.v[p];
         if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + kp.off_best + p] = s.v[p];
@@ -194,7 +266,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         keys[j] = key;
     }
     __syncthreads();
-    bitonic_sort_u64(keys, npow);
+    bitonic_sort_u64<NT>(keys, npow);
     const int k = K < kp.N ? K : kp.N;                     // argsort(costs)[:k]
     int *out_elite = reinterpret_cast<int *>(out + kp.off_out_elite);
     for (int j = t; j < K; j += TB) {
@@ -270,7 +342,9 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
     const Smem s(smem_raw, kp);
     const int t = threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
     __shared__ int s_last;
-    stage_inputs(kp, r, s);
+    if (blk == 0) phase_mark(kp, 0);
+    stage_inputs<TB>(kp, r, s);
+    if (blk == 0) phase_mark(kp, 1);
     const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + t;
@@ -303,6 +377,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
                 for (int p = 0; p < kp.P; ++p) tcol[p * TS] = 0.0f;
             }
         }
+        if (blk == 0 && it == 0) phase_mark(kp, 2);
         // ---- 2. rollout + cost ----
         float cost = CUDART_INF_F;
         if (active) {
@@ -318,17 +393,18 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
             kp.costs[(size_t)r * kp.n_local + local] = cost;
         }
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }
+        if (blk == 0 && it == 0) phase_mark(kp, 3);
         // ---- 3. tile reduction folded into the block's running record ----
         float cmin = cost;
         int imin = active ? gi : 0x7fffffff;
-        block_argmin(cmin, imin, s.red);
+        block_argmin<TB>(cmin, imin, s.red);
         if (METHOD != RANDOM_SAMPLING) {
             const float m_new = fminf(m_run, cmin);              // cmin is finite: the tile has >= 1 active sample
             const float scale_old = (m_run == CUDART_INF_F) ? 0.0f : expf(-(m_run - m_new));
             const float w = active ? expf(-(cost - m_new)) : 0.0f;   // exp(-(c - beta)/T), T = 1, S:828-830
             __syncthreads();
             s.w[t] = w;
-            const float s_tile = block_sum(w, s.red);            // barriers inside publish s.w and the tile
+            const float s_tile = block_sum<TB>(w, s.red);            // barriers inside publish s.w and the tile
             s_run = fmaf(s_run, scale_old, s_tile);
             for (int p = t; p < kp.P; p += TB) {
                 const float *rowp = s.tile + p * TS;
@@ -345,6 +421,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         __syncthreads();
     }
     if (kp.mode == MODE_ROLLOUT) return;
+    if (blk == 0) phase_mark(kp, 4);
     float *rec = kp.blk_recs + ((size_t)r * kp.nblk + blk) * kp.blk_rec_stride;
     if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
@@ -356,15 +433,31 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         s_last = (ticket == (unsigned int)(kp.nblk - 1));
     }
     __syncthreads();
+    if (blk == 0) phase_mark(kp, 5);
     if (!s_last) return;
     __threadfence();
-    shard_reduce<METHOD>(kp, r, s);
+    phase_mark(kp, 8);
+    float M, S; int IDX;
+    shard_reduce<METHOD, TB>(kp, r, s, M, IDX, S);
+    phase_mark(kp, 9);
     if (kp.fused_finish) {
         __threadfence();
         __syncthreads();
-        finish<PARAM, ADAPTIVE, METHOD>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0);
+        finish<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
     }
+    phase_mark(kp, 11);
     if (t == 0) kp.counters[r] = 0u;
+}
+
+// Step 6 alone: merges `world` gathered shard records (sample-sharded controllers).  grid = (1, R).
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__global__ void __launch_bounds__(TB, 4) finish_kernel(const __grid_constant__ KParams kp) {
+    extern __shared__ __align__(16) float smem_raw[];
+    const Smem s(smem_raw, kp);
+    const int r = blockIdx.y;
+    stage_inputs<TB>(kp, r, s);
+    finish<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, kp.shard_recv + (size_t)r * kp.shard_rec_stride, kp.world,
+                                    (size_t)gridDim.y * kp.shard_rec_stride);
 }
 
 }  // namespace qp

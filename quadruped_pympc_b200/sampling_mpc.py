@@ -68,6 +68,7 @@ def make_c_config(cfg: SamplerConfig, num_robots=1, shard_rank=0, shard_world=1)
     c.sigma_mppi = float(cfg.sigma_mppi)
     c.step_freq_available[:] = [float(x) for x in cfg.step_freq_available]
     c.pgg_duty_factor = 0.65                                                        # A:179
+    c.lanes_per_sample = int(cfg.lanes_per_sample)
     return c
 
 

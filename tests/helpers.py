@@ -11,11 +11,13 @@ KNOT_RTOL = 1e-4      # returned GRFs / knots (plus a small absolute floor for v
 
 PARAMS = ['zero_order', 'linear_spline', 'cubic_spline']
 METHODS = ['random_sampling', 'mppi', 'cem_mppi']
+LANES = [1, 4]      # kernel variants: sample per thread | four lanes per sample
 
 
 def make_pair(robot='go2', N=1000, **kw):
     """(oracle, controller, oracle_cfg) for the same configuration."""
-    ocfg = OracleConfig.for_robot(robot, num_parallel_computations=N, **kw)
+    okw = {k: v for k, v in kw.items() if k != 'lanes_per_sample'}     # kernel variant: product-only key
+    ocfg = OracleConfig.for_robot(robot, num_parallel_computations=N, **okw)
     pcfg = qp.SamplerConfig.for_robot(robot, num_parallel_computations=N, **kw)
     return SamplingOracle(ocfg), qp.Sampling_MPC(pcfg), ocfg
 

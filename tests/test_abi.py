@@ -42,7 +42,7 @@ def test_config_struct_layout_matches_defaults(built):
     lib = _lib.load()
     c = _lib.QpmpcConfig()
     lib.qpmpc_config_defaults(C.byref(c))
-    assert (c.abi_version, c.num_samples, c.horizon, c.num_splines) == (1, 10000, 12, 2)
+    assert (c.abi_version, c.num_samples, c.horizon, c.num_splines) == (2, 10000, 12, 2)
     assert c.parametrization == _lib.PARAMETRIZATION['cubic_spline'] and c.method == _lib.METHOD['random_sampling']
     assert c.seed == 42 and abs(c.mass - 15.019) < 1e-6 and abs(c.pgg_duty_factor - 0.65) < 1e-7
     assert list(c.q_diag) == [0, 0, 1500, 200, 200, 200, 500, 500, 0, 20, 20, 50]

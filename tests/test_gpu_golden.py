@@ -13,11 +13,12 @@ pytestmark = pytest.mark.gpu
 FIXTURES = tick_fixtures()
 
 
+@pytest.mark.parametrize('lanes', [1, 4])
 @pytest.mark.parametrize('path', FIXTURES, ids=fixture_id)
-def test_cuda_tick_reproduces_reference(built, path):
+def test_cuda_tick_reproduces_reference(built, path, lanes):
     fx = Fixture(path)
     orc = fx.oracle()
-    ctrl = qp.Sampling_MPC(qp.SamplerConfig.for_robot(fx.robot, **fx.config_kwargs()))
+    ctrl = qp.Sampling_MPC(qp.SamplerConfig.for_robot(fx.robot, lanes_per_sample=lanes, **fx.config_kwargs()))
     sc, z = fx.scenario(), fx.z
     noise, freqs, sigma = fx.noise(orc), fx.step_freqs(orc), fx.sigma()
     tail = (sc['phase_signal'], sc['nominal_step_freq'], int(z['optimize_swing']))
@@ -39,15 +40,16 @@ def test_cuda_tick_reproduces_reference(built, path):
         np.testing.assert_allclose(out[7], exp['new_sigma_cem_mppi'], rtol=KNOT_RTOL, atol=1e-6)
 
 
+@pytest.mark.parametrize('lanes', [1, 4])
 @pytest.mark.parametrize('path', FIXTURES, ids=fixture_id)
-def test_cuda_rollout_seam_reproduces_reference(built, path):
+def test_cuda_rollout_seam_reproduces_reference(built, path, lanes):
     """jit_vectorized_rollout (S:176-177 / A:186-187): explicit parameters in, raw costs out."""
     fx = Fixture(path)
     z = fx.z
     params = z['seam_params']
     kw = fx.config_kwargs()
     kw['num_parallel_computations'] = params.shape[0]
-    ctrl = qp.Sampling_MPC(qp.SamplerConfig.for_robot(fx.robot, **kw))
+    ctrl = qp.Sampling_MPC(qp.SamplerConfig.for_robot(fx.robot, lanes_per_sample=lanes, **kw))
     if fx.adaptive:
         got = ctrl.jit_vectorized_rollout(z['state'], z['reference'], z['phase_signal'], params, z['seam_freqs'])
     else:

@@ -6,20 +6,21 @@ import numpy as np
 import pytest
 
 from quadruped_pympc_b200 import synthetic
-from helpers import (PARAMS, METHODS, make_pair, seeded_noise, seeded_freqs, run_both, assert_tick_parity,
+from helpers import (PARAMS, METHODS, LANES, make_pair, seeded_noise, seeded_freqs, run_both, assert_tick_parity,
                      COST_RTOL)
 
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize('lanes', LANES)
 @pytest.mark.parametrize('adaptive', [False, True])
 @pytest.mark.parametrize('method', METHODS)
 @pytest.mark.parametrize('param', PARAMS)
-def test_tick_parity_injected_noise(built, param, method, adaptive):
+def test_tick_parity_injected_noise(built, param, method, adaptive, lanes):
     """3 parametrisations x 3 control laws x {fixed, adaptive}; N deliberately not a multiple of the tile (128)."""
     N = 1337
     oracle, ctrl, _ = make_pair('go2', N, control_parametrization=param, sampling_method=method,
-                                optimize_step_freq=adaptive)
+                                optimize_step_freq=adaptive, lanes_per_sample=lanes)
     for seed, gait in [(1, 'trot'), (7, 'pace')]:
         sc = synthetic.scenario('go2', gait, seed=seed)
         rng = np.random.RandomState(seed)
@@ -31,12 +32,14 @@ def test_tick_parity_injected_noise(built, param, method, adaptive):
         assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
 
 
+@pytest.mark.parametrize('lanes', LANES)
 @pytest.mark.parametrize('adaptive', [False, True])
 @pytest.mark.parametrize('param', PARAMS)
-def test_rollout_seam(built, param, adaptive):
+def test_rollout_seam(built, param, adaptive, lanes):
     """jit_vectorized_rollout (S:176-177 / A:186-187): explicit parameters in, raw costs out."""
     N = 600
-    oracle, ctrl, _ = make_pair('aliengo', N, control_parametrization=param, optimize_step_freq=adaptive)
+    oracle, ctrl, _ = make_pair('aliengo', N, control_parametrization=param, optimize_step_freq=adaptive,
+                                lanes_per_sample=lanes)
     sc = synthetic.scenario('aliengo', 'trot', seed=11)
     rng = np.random.RandomState(5)
     params = (4.0 * rng.randn(N, oracle.P)).astype(np.float32)
@@ -50,9 +53,11 @@ def test_rollout_seam(built, param, adaptive):
     np.testing.assert_allclose(got, want, rtol=COST_RTOL)
 
 
-def test_config2_full_size(built):
+@pytest.mark.parametrize('lanes', LANES)
+def test_config2_full_size(built, lanes):
     """BASELINE config 2 at full size: Go2 trot, MPPI, cubic, N = 10,000 with injected noise."""
-    oracle, ctrl, _ = make_pair('go2', 10000, control_parametrization='cubic_spline', sampling_method='mppi')
+    oracle, ctrl, _ = make_pair('go2', 10000, control_parametrization='cubic_spline', sampling_method='mppi',
+                                lanes_per_sample=lanes)
     sc = synthetic.scenario('go2', 'trot', seed=0)
     best0 = np.zeros(oracle.P, np.float32)
     noise = seeded_noise(oracle, 0)
@@ -60,9 +65,11 @@ def test_config2_full_size(built):
     assert_tick_parity(ref, got)
 
 
-def test_config1_full_size(built):
+@pytest.mark.parametrize('lanes', LANES)
+def test_config1_full_size(built, lanes):
     """BASELINE config 1: Aliengo trot, random_sampling, zero-order, N = 10,000."""
-    oracle, ctrl, _ = make_pair('aliengo', 10000, control_parametrization='zero_order', sampling_method='random_sampling')
+    oracle, ctrl, _ = make_pair('aliengo', 10000, control_parametrization='zero_order', sampling_method='random_sampling',
+                                lanes_per_sample=lanes)
     sc = synthetic.scenario('aliengo', 'trot', seed=2)
     best0 = np.zeros(oracle.P, np.float32)
     noise = seeded_noise(oracle, 2)
@@ -70,10 +77,12 @@ def test_config1_full_size(built):
     assert_tick_parity(ref, got)
 
 
-def test_philox_tick_matches_oracle_on_exported_noise(built):
+@pytest.mark.parametrize('lanes', LANES)
+def test_philox_tick_matches_oracle_on_exported_noise(built, lanes):
     """Production mode (in-kernel Philox): the tick must equal the oracle fed with the noise the device exports."""
     for method in METHODS:
-        oracle, ctrl, _ = make_pair('go2', 3000, control_parametrization='cubic_spline', sampling_method=method)
+        oracle, ctrl, _ = make_pair('go2', 3000, control_parametrization='cubic_spline', sampling_method=method,
+                                    lanes_per_sample=lanes)
         sc = synthetic.scenario('go2', 'trot', seed=4)
         ctrl.with_newkey()
         key = ctrl.master_key.copy()
