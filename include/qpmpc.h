@@ -46,7 +46,11 @@ typedef enum { QPMPC_RANDOM_SAMPLING = 0, QPMPC_MPPI = 1, QPMPC_CEM_MPPI = 2 } q
 /* Host<->device transport of the per-tick packet (inputs ~1 KB, outputs ~1 KB). */
 typedef enum {
     QPMPC_IO_MEMCPY = 0,  /* pinned staging + cudaMemcpyAsync H2D / D2H around the kernel */
-    QPMPC_IO_MAPPED = 1   /* kernel reads/writes mapped pinned host memory directly (zero-copy over PCIe) */
+    QPMPC_IO_MAPPED = 1,  /* kernel reads/writes mapped pinned host memory directly (zero-copy over PCIe) */
+    QPMPC_IO_DIRECT = 2   /* default for one controller: the tick packet travels in the kernel's parameter space, the last
+                             block stores the result packet + a completion stamp to mapped pinned host memory and the host
+                             spins on the stamp -- no copy-engine hop and no stream synchronisation around the kernel.
+                             Falls back to QPMPC_IO_MEMCPY for batched / sharded handles and oversized packets. */
 } qpmpc_io_mode;
 
 /* Everything Sampling_MPC.__init__ (S:23-177 / A:24-187) and Centroidal_Model_JAX.__init__ (M:20-65) freeze. */

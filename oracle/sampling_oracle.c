@@ -375,40 +375,17 @@ static inline float u01_from_bits(uint32_t b) {       /* mantissa trick of jax.r
 }
 
 /* Giles, "Approximating the erfinv function" (single precision) -- the polynomial XLA's erf_inv uses */
-static inline float erfinv_giles(float x) {
-    float w = -logf((1.0f - x) * (1.0f + x));
-    float p;
-    if (w < 5.0f) {
-        w = w - 2.5f;
-        p = 2.81022636e-08f;
-        p = 3.43273939e-07f + p * w;
-        p = -3.5233877e-06f + p * w;
-        p = -4.39150654e-06f + p * w;
-        p = 0.00021858087f + p * w;
-        p = -0.00125372503f + p * w;
-        p = -0.00417768164f + p * w;
-        p = 0.246640727f + p * w;
-        p = 1.50140941f + p * w;
-    } else {
-        w = sqrtf(w) - 3.0f;
-        p = -0.000200214257f;
-        p = 0.000100950558f + p * w;
-        p = 0.00134934322f + p * w;
-        p = -0.00367342844f + p * w;
-        p = 0.00573950773f + p * w;
-        p = -0.0076224613f + p * w;
-        p = 0.00943887047f + p * w;
-        p = 1.00167406f + p * w;
-        p = 2.83297682f + p * w;
-    }
-    return p * x;
-}
-
-static inline float normal_from_bits(uint32_t b) {    /* jax.random.normal: sqrt(2)*erfinv(uniform(-1+eps,1)) */
-    const float lo = -0.99999994f;                      /* nextafter(-1, 0) */
-    float u = u01_from_bits(b) * 2.0f + lo;
-    u = u > lo ? u : lo;
-    return 1.41421356f * erfinv_giles(u);
+/* Box-Muller exactly as the device does it (csrc/qpmpc_kernels.cuh box_muller), with libm in place of the SFU
+ * approximations: two words -> two standard normals. */
+static inline void box_muller(uint32_t a, uint32_t b, float *z0, float *z1) {
+    union { uint32_t u; float f; } ua, ub;
+    ua.u = (a >> 9) | 0x3F800000u;
+    ub.u = (b >> 9) | 0x40000000u;
+    float u = 2.0f - ua.f;
+    float th = ub.f * 3.14159265f + -9.42477796f;
+    float r = sqrtf(-1.38629436f * log2f(u));
+    *z0 = r * cosf(th);
+    *z1 = r * sinf(th);
 }
 
 /* additional_random_parameters (N,P) for one tick; sigma (P) used by cem_mppi only.  Row/segment mapping:
@@ -430,6 +407,9 @@ void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_
         for (int qd = 0; qd < P / 4; ++qd) {
             uint32_t ctr[4] = {(uint32_t)qd, (uint32_t)j, tick, 0u}, key[2] = {seed, robot}, r[4];
             orc_philox4x32_10(ctr, key, r);
+            float z[4];
+            box_muller(r[0], r[1], &z[0], &z[1]);
+            box_muller(r[2], r[3], &z[2], &z[3]);
             for (int e = 0; e < 4; ++e) {
                 int p = 4 * qd + e;
                 float v;
@@ -438,9 +418,9 @@ void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_
                         float s2 = c->sigma_rs[2];
                         v = u01_from_bits(r[e]) * (s2 - (-s2)) + (-s2);
                         v = v > -s2 ? v : -s2;
-                    } else v = c->sigma_rs[seg] * normal_from_bits(r[e]);
-                } else if (c->method == ORC_MPPI) v = c->sigma_mppi * normal_from_bits(r[e]);
-                else v = normal_from_bits(r[e]) * sigma[p];
+                    } else v = c->sigma_rs[seg] * z[e];
+                } else if (c->method == ORC_MPPI) v = c->sigma_mppi * z[e];
+                else v = z[e] * sigma[p];
                 row[p] = v;
             }
         }

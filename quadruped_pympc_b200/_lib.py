@@ -20,7 +20,7 @@ QPMPC_ABI_VERSION = 2
 MAX_HORIZON, MAX_SPLINES, MAX_ELITE = 64, 16, 256
 PARAMETRIZATION = {'zero_order': 0, 'linear_spline': 1, 'cubic_spline': 2}
 METHOD = {'random_sampling': 0, 'mppi': 1, 'cem_mppi': 2}
-IO_MODE = {'memcpy': 0, 'mapped': 1}
+IO_MODE = {'memcpy': 0, 'mapped': 1, 'direct': 2}
 OK, ERR_INVALID, ERR_CUDA, ERR_NCCL, ERR_STATE = 0, -1, -2, -3, -4
 
 
@@ -93,7 +93,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for u in units:
         obj = os.path.join(obj_dir, u[:-3] + '.o')
-        cmd = ['nvcc'] + NVCC_COMPILE_FLAGS + (['-Xptxas', '-v'] if verbose else []) + \
+        cmd = ['nvcc'] + NVCC_COMPILE_FLAGS + os.environ.get('QPMPC_NVCC_EXTRA', '').split() + \
+              (['-Xptxas', '-v'] if verbose else []) + \
               ['-c', os.path.join(CSRC, u), '-o', obj]
         procs.append((u, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     objs = []

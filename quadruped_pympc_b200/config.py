@@ -58,7 +58,7 @@ class SamplerConfig:
     # --- keys that only exist for this backend ---
     device: int = 0                  # CUDA ordinal (the reference's 'device': 'gpu'|'cpu' has no CPU meaning here)
     seed: int = 42                   # jax.random.PRNGKey(42), S/centroidal_nmpc_jax.py:167
-    io_mode: str = 'memcpy'          # 'memcpy' | 'mapped'
+    io_mode: str = 'direct'          # 'direct' (packet in kernel params, result stamped into mapped host memory) | 'memcpy' | 'mapped'
     use_graph: bool = True
     elite_k: int = 0                 # 0 = reference default (10 / 200)
     lanes_per_sample: int = 0        # kernel variant: 0 = auto, 1 = sample per thread, 4 = four lanes per sample

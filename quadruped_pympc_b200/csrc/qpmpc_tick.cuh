@@ -33,7 +33,7 @@ __host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB,
 template <int NT>
 __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Smem &s) {
     constexpr int TB = NT;
-    const float *gin = kp.in + (size_t)r * kp.in_stride;
+    const float *gin = kp.param_packet ? kp.packet : kp.in + (size_t)r * kp.in_stride;
     for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
     __syncthreads();
     if (threadIdx.x < kp.H) {       // gravity compensation per step, S:377-380
@@ -333,6 +333,20 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     }
 }
 
+// Direct I/O epilogue (last block, one controller): copy the finished result packet to mapped pinned host memory and
+// stamp it; the host spins on the stamp instead of waiting for a D2H copy + stream synchronisation.
+__device__ __forceinline__ void publish_to_host(const KParams &kp, int r) {
+    if (kp.host_out == nullptr) return;
+    __syncthreads();                                   // the packet in kp.out was written by this block
+    if (threadIdx.x < 32) {
+        const float *o = kp.out + (size_t)r * kp.out_stride;
+        for (int k = threadIdx.x; k < kp.out_stride; k += 32) kp.host_out[k] = o[k];
+        __threadfence_system();
+        __syncwarp();
+        if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned int *>(kp.host_out + kp.out_stride) = kp.seq;
+    }
+}
+
 // ======================================================================================================
 // The tick kernel.  grid = (nblk, R), block = TB.  dynamic smem = smem_floats(...) * 4 bytes.
 // ======================================================================================================
@@ -444,6 +458,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         __threadfence();
         __syncthreads();
         finish<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
+        publish_to_host(kp, r);
     }
     phase_mark(kp, 11);
     if (t == 0) kp.counters[r] = 0u;

@@ -94,37 +94,59 @@ class LazyCosts:
 
 
 class _TickBuffers:
-    """ctypes in/out structs plus the numpy arrays that back their pointers (kept alive together)."""
+    """ctypes in/out structs bound ONCE to preallocated float32 staging arrays: a tick only copies values into them
+    (no allocation, no pointer re-binding on the tick path).  Views onto the fixed-size members of the out struct let
+    `_unpack` copy results without going through Python lists."""
 
-    def __init__(self, P, elite_k):
+    def __init__(self, P, elite_k, H):
         self.cin, self.cout = _lib.QpmpcTickIn(), _lib.QpmpcTickOut()
-        self.best_out = np.zeros(P, np.float32)
-        self.sigma_out = np.zeros(P, np.float32)
+        self.H = H
+        self.state, self.reference = np.zeros(24, np.float32), np.zeros(24, np.float32)
+        self.contact = np.zeros((4, H), np.float32)
+        self.best_in, self.sigma_in = np.zeros(P, np.float32), np.zeros(P, np.float32)
+        self.timing = np.zeros(4, np.float32)
+        self.best_out, self.sigma_out = np.zeros(P, np.float32), np.zeros(P, np.float32)
         self.elite = np.full(max(elite_k, 1), -1, np.int32)
-        self.cout.best = _fp(self.best_out)
-        self.cout.sigma_new = _fp(self.sigma_out)
-        self.cout.elite_indices = self.elite.ctypes.data_as(C.POINTER(C.c_int32))
+        i, o = self.cin, self.cout
+        i.state, i.reference, i.contact_sequence, i.contact_ld = _fp(self.state), _fp(self.reference), _fp(self.contact), H
+        i.best = _fp(self.best_in)
+        self._p_sigma, self._p_timing = _fp(self.sigma_in), _fp(self.timing)
+        o.best, o.sigma_new = _fp(self.best_out), _fp(self.sigma_out)
+        o.elite_indices = self.elite.ctypes.data_as(C.POINTER(C.c_int32))
+        self.grfs_view = np.ctypeslib.as_array(o.grfs)
+        self.pred_view = np.ctypeslib.as_array(o.predicted_state)
         self.keep = []
 
     def fill(self, state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing, noise,
              step_freqs, H):
-        cs = _f32(contact_sequence)
+        cs = np.asarray(contact_sequence)
         if cs.ndim != 2 or cs.shape[0] != 4 or cs.shape[1] < H:
             raise _lib.QpmpcError(_lib.ERR_INVALID, f'contact_sequence must be (4, >= {H}), got {cs.shape}')
-        st, rf, bs = _f32(state, (24,)), _f32(reference, (24,)), _f32(best)
-        sg = _f32(sigma) if sigma is not None else None
-        tm = _f32(timing, (4,)) if timing is not None else None
-        nz = _f32(noise) if noise is not None else None
-        fq = _f32(step_freqs) if step_freqs is not None else None
-        self.keep = [cs, st, rf, bs, sg, tm, nz, fq]
+        self.contact[...] = cs[:, :H]                       # only [:, :H] is read (FULL_STANCE tables are (4, 2H))
+        try:
+            self.state[...] = state
+            self.reference[...] = reference
+        except ValueError:                                  # e.g. (24, 1) columns
+            self.state[...] = np.asarray(state).reshape(24)
+            self.reference[...] = np.asarray(reference).reshape(24)
+        self.best_in[...] = best
         i = self.cin
-        i.state, i.reference, i.contact_sequence, i.contact_ld = _fp(st), _fp(rf), _fp(cs), cs.shape[1]
-        i.best, i.sigma, i.phase_signal = _fp(bs), _fp(sg), _fp(tm)
+        if sigma is not None:
+            self.sigma_in[...] = sigma
+            i.sigma = self._p_sigma
+        else:
+            i.sigma = None
+        if timing is not None:
+            self.timing[...] = timing
+            i.phase_signal = self._p_timing
+        else:
+            i.phase_signal = None
         i.nominal_step_freq = float(nominal) if nominal is not None else 0.0
         i.optimize_swing = int(optimize_swing) if optimize_swing is not None else 0
-        k = np.asarray(key).astype(np.uint64).ravel()
-        i.key[0], i.key[1] = int(k[0]) & 0xFFFFFFFF, int(k[1]) & 0xFFFFFFFF
-        i.noise, i.step_freqs = _fp(nz), _fp(fq)
+        k0, k1 = key.tolist() if isinstance(key, np.ndarray) else key
+        i.key[0], i.key[1] = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
+        self.keep = [noise, step_freqs]                     # parity hooks only; already float32 C-contiguous
+        i.noise, i.step_freqs = _fp(noise), _fp(step_freqs)
 
 
 class Sampling_MPC:
@@ -171,6 +193,7 @@ class Sampling_MPC:
         self._buf = None
         self._tick_serial = 0
         self._n_local = None
+        self._cem = cfg.sampling_method == 'cem_mppi'
         self.jitted_compute_control = self.compute_control
 
     # ------------------------------------------------------------------ handle management
@@ -184,7 +207,7 @@ class Sampling_MPC:
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
         self._n_local = lib.qpmpc_num_local_samples(h)
-        self._buf = _TickBuffers(self.num_control_parameters, self.elite_k)
+        self._buf = _TickBuffers(self.num_control_parameters, self.elite_k, self.horizon)
         return h
 
     def close(self):
@@ -224,8 +247,6 @@ class Sampling_MPC:
         """Rollouts + local reduction of this shard's slice; returns the shard record (floats) for a caller-side gather
         (tests, or transports other than NCCL)."""
         h, lib, b = self._ensure(), _lib.load(), self._buf
-        if self.sampling_method == 'cem_mppi':
-            sigma = np.broadcast_to(np.asarray(sigma, dtype=np.float32), (self.num_control_parameters,)).copy()
         b.fill(state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing,
                None if noise is None else _f32(noise), None if step_freqs is None else _f32(step_freqs), self.horizon)
         self._tick_serial += 1
@@ -341,22 +362,27 @@ class Sampling_MPC:
             (state, reference, contact_sequence, best, key, sigma, [timing, nominal_step_frequency, [optimize_swing]])
             -> (nmpc_GRFs, nmpc_footholds, nmpc_predicted_state, best, best_cost, best_freq, costs, new_sigma)
         """
-        cem = self.sampling_method == 'cem_mppi'
-        names = ['sigma', 'timing', 'nominal_step_frequency', 'optimize_swing'] if cem else \
-                ['timing', 'nominal_step_frequency', 'optimize_swing']
-        vals = dict(zip(names, args))
-        if len(args) > len(names):
-            raise TypeError(f'compute_control() takes at most {5 + len(names)} positional arguments')
-        for k, v in kwargs.items():
-            if k not in names:
-                raise TypeError(f"compute_control() got an unexpected keyword argument '{k}'")
-            vals[k] = v
-        sigma = vals.get('sigma')
-        timing, nominal, optimize_swing = vals.get('timing'), vals.get('nominal_step_frequency'), vals.get('optimize_swing')
-        if cem:
-            if sigma is None:
-                raise TypeError("compute_control_cem_mppi() missing required argument 'sigma'")
-            sigma = np.broadcast_to(np.asarray(sigma, dtype=np.float32), (self.num_control_parameters,)).copy()
+        cem = self._cem
+        if not kwargs and len(args) == (4 if cem else 3):        # the call the interface makes (I:131-168): fast path
+            if cem:
+                sigma, timing, nominal, optimize_swing = args
+            else:
+                sigma = None
+                timing, nominal, optimize_swing = args
+        else:
+            names = ['sigma', 'timing', 'nominal_step_frequency', 'optimize_swing'] if cem else \
+                    ['timing', 'nominal_step_frequency', 'optimize_swing']
+            vals = dict(zip(names, args))
+            if len(args) > len(names):
+                raise TypeError(f'compute_control() takes at most {5 + len(names)} positional arguments')
+            for k, v in kwargs.items():
+                if k not in names:
+                    raise TypeError(f"compute_control() got an unexpected keyword argument '{k}'")
+                vals[k] = v
+            sigma = vals.get('sigma')
+            timing, nominal, optimize_swing = vals.get('timing'), vals.get('nominal_step_frequency'), vals.get('optimize_swing')
+        if cem and sigma is None:
+            raise TypeError("compute_control_cem_mppi() missing required argument 'sigma'")
         if self.adaptive and (timing is None or nominal is None or (optimize_swing is None and step_freqs is None)):
             raise TypeError('the gait-adaptive controller needs timing, nominal_step_frequency and optimize_swing '
                             '(A:326,637-638,972-974)')
@@ -388,8 +414,8 @@ class Sampling_MPC:
 
     def _unpack(self, b):
         o = b.cout
-        grfs = np.array(o.grfs[:], dtype=np.float32)
-        pred = np.array(o.predicted_state[:], dtype=np.float32)
+        grfs = b.grfs_view.copy()
+        pred = b.pred_view.copy()
         footholds = np.zeros(12, dtype=np.int32)                    # S:748
         best = b.best_out.copy()
         self.last_best_index = int(o.best_index)

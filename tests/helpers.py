@@ -57,20 +57,38 @@ def run_both(oracle, ctrl, sc, best0, noise, sigma=None, freqs=None, optimize_sw
     out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *args,
                                       noise=noise, step_freqs=freqs if adaptive else None)
     got = dict(nmpc_GRFs=out[0], nmpc_footholds=out[1], nmpc_predicted_state=out[2], best_control_parameters=out[3],
-               best_cost=out[4], best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
+               best_cost=out[4], best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index,
+               _noise=noise)
     if cem:
         got['new_sigma_cem_mppi'] = out[7]
         got['elite_indices'] = ctrl.last_elite_indices
     return ref, got
 
 
-def assert_tick_parity(ref, got, cem=False):
+def knot_atol(ref_costs, got_costs, weights, noise, floor=2e-4):
+    """Absolute tolerance for the MPPI-updated knots (and the GRFs read out of them).
+
+    best_new = best + sum_i w_i eps_i with w = softmax(-c) (S:828-836) amplifies cost perturbations: to first order
+    |d best_p| <= 2 * max_i|dc_i| * sum_i w_i |eps_ip|.  The north_star allows rel 1e-5 on the costs, so the knots can
+    only be held to `floor` PLUS that propagated bound, evaluated with the cost differences actually observed (they
+    are ~1e-7 relative in practice, which keeps this term around 1e-5 .. 1e-3 depending on how close the best two
+    samples are).  For random_sampling (no weights) the bound is the floor alone."""
+    if weights is None or noise is None:
+        return floor
+    dc = float(np.max(np.abs(np.asarray(got_costs, np.float64) - np.asarray(ref_costs, np.float64))))
+    amp = float(np.max(np.abs(noise).T.astype(np.float64) @ np.asarray(weights, np.float64)))
+    return floor + 2.0 * dc * amp
+
+
+def assert_tick_parity(ref, got, cem=False, noise=None):
     rel = np.max(np.abs(got['costs'] - ref['costs']) / np.maximum(np.abs(ref['costs']), 1e-12))
     assert rel < COST_RTOL, f'cost rel err {rel:.3e} >= {COST_RTOL}'
     assert got['best_index'] == ref['best_index'], (got['best_index'], ref['best_index'])
     np.testing.assert_allclose(got['best_cost'], ref['best_cost'], rtol=COST_RTOL)
-    np.testing.assert_allclose(got['best_control_parameters'], ref['best_control_parameters'], rtol=KNOT_RTOL, atol=2e-4)
-    np.testing.assert_allclose(got['nmpc_GRFs'], ref['nmpc_GRFs'], rtol=KNOT_RTOL, atol=2e-4)
+    noise = got.get('_noise') if noise is None else noise
+    atol = knot_atol(ref['costs'], got['costs'], ref.get('weights'), noise)
+    np.testing.assert_allclose(got['best_control_parameters'], ref['best_control_parameters'], rtol=KNOT_RTOL, atol=atol)
+    np.testing.assert_allclose(got['nmpc_GRFs'], ref['nmpc_GRFs'], rtol=KNOT_RTOL, atol=atol)
     np.testing.assert_allclose(got['nmpc_predicted_state'], ref['nmpc_predicted_state'], rtol=KNOT_RTOL, atol=1e-6)
     np.testing.assert_allclose(got['best_freq'], ref['best_freq'], rtol=1e-6)
     if cem:

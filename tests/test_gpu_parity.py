@@ -29,7 +29,7 @@ def test_tick_parity_injected_noise(built, param, method, adaptive, lanes):
         noise = seeded_noise(oracle, seed, sigma)
         freqs = seeded_freqs(oracle, seed) if adaptive else None
         ref, got = run_both(oracle, ctrl, sc, best0, noise, sigma=sigma, freqs=freqs)
-        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
 
 
 @pytest.mark.parametrize('lanes', LANES)
@@ -97,4 +97,24 @@ def test_philox_tick_matches_oracle_on_exported_noise(built, lanes):
                    best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
         if method == 'cem_mppi':
             got['new_sigma_cem_mppi'], got['elite_indices'] = out[7], ctrl.last_elite_indices
-        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
+
+
+@pytest.mark.parametrize('method', METHODS)
+def test_device_noise_matches_host_mirror(built, method):
+    """The in-kernel generator (Philox4x32-10 + Box-Muller on the SFU) vs its host mirror in oracle/sampling_oracle.c
+    (same integer stream, libm instead of the SFU approximations) and the distribution the reference asks for."""
+    from oracle import c_oracle
+    N = 6000
+    oracle, ctrl, ocfg = make_pair('go2', N, control_parametrization='cubic_spline', sampling_method=method)
+    key = np.array([42, 5], np.uint32)
+    sigma = np.linspace(0.5, 4.0, oracle.P).astype(np.float32) if method == 'cem_mppi' else None
+    dev = ctrl.generate_noise(key, sigma)
+    host = c_oracle.COracle(ocfg).noise(42, 5, sigma=sigma)
+    np.testing.assert_allclose(dev, host, rtol=0, atol=2e-4)
+    assert np.all(dev[0] == 0.0)
+    if method == 'mppi':
+        z = dev[1:] / 3.0
+        assert abs(z.mean()) < 5e-3 and abs(z.std() - 1) < 5e-3
+        assert abs(np.mean(z ** 4) - 3.0) < 0.05                  # kurtosis of a normal
+        assert abs(np.corrcoef(z[:, 0], z[:, 1])[0, 1]) < 0.05    # the two Box-Muller outputs are uncorrelated

@@ -42,7 +42,7 @@ def test_sharded_tick_equals_oracle(built, method, adaptive, world):
                    best_freq=o[5], costs=costs, best_index=s.last_best_index)
         if method == 'cem_mppi':
             got['new_sigma_cem_mppi'], got['elite_indices'] = o[7], s.last_elite_indices
-        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'))
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
     # every shard computed the identical result (deterministic merge in rank order)
     for o in outs[1:]:
         assert np.array_equal(o[3], outs[0][3]) and np.array_equal(o[0], outs[0][0])

@@ -54,7 +54,7 @@ def fmt_phases(ph):
     return ' '.join(f'{names[k]}@{(ph[k] - b0) / 1e3:.1f}' for k in sorted(names) if ph[k] > 0)
 
 
-def e2e(method='mppi', param='cubic_spline', N=10000, lanes=0, io_mode='memcpy', use_graph=True, ticks=2000):
+def e2e(method='mppi', param='cubic_spline', N=10000, lanes=0, io_mode='direct', use_graph=True, ticks=2000):
     cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization=param,
                                      num_parallel_computations=N, io_mode=io_mode, use_graph=use_graph, lanes_per_sample=lanes)
     c = qp.Sampling_MPC(cfg)
@@ -88,6 +88,9 @@ if __name__ == '__main__':
     tf = C.c_float(0)
     _lib.check(_lib.load().qpmpc_measure_fp32_peak(0, C.byref(tf)))
     print('fp32 peak TFLOP/s', tf.value, flush=True)
+    if what in ('one4', 'one1'):
+        ms, ph = resident(lanes=int(what[3]), steps=10)
+        print(f'config2 lanes={what[3]}: kernel {ms * 1e3:.1f} us | {fmt_phases(ph)}', flush=True)
     if what in ('quick', 'phases'):
         for lanes in (1, 4):
             ms, ph = resident(lanes=lanes)
@@ -114,5 +117,5 @@ if __name__ == '__main__':
     if what in ('quick', 'e2e'):
         for lanes in (1, 4):
             e2e(lanes=lanes)
-        e2e(lanes=4, use_graph=False)
-        e2e(lanes=4, io_mode='mapped', use_graph=False)
+        e2e(lanes=1, io_mode='memcpy')
+        e2e(lanes=1, io_mode='memcpy', use_graph=False)
