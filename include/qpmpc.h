@@ -168,7 +168,18 @@ int qpmpc_shard_get_record(qpmpc_handle *h, float *host_rec);                /* 
 /* NCCL plumbing (dlopen of libnccl.so.2; no link-time dependency).  id: 128-byte ncclUniqueId. */
 int qpmpc_nccl_unique_id(const char *libnccl_path, unsigned char id[128]);
 int qpmpc_shard_init_nccl(qpmpc_handle *h, const char *libnccl_path, const unsigned char id[128]);
-int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out); /* partial+allgather+finish */
+/* Peer exchange (2..8 shards on one NVSwitch node): the collective is fused into the tick kernel.  Each rank exports
+ * a 128-byte blob describing its mailbox (CUDA IPC handle; or the raw pointer when the ranks are threads of one
+ * process), the launcher all-gathers the blobs (torch.distributed / MPI / a pipe), every rank attaches all of them in
+ * rank order.  From then on qpmpc_tick_sharded is ONE launch per rank: rollouts + local reduction, the last block
+ * stores its record into every peer's mailbox over NVLink, waits for the peers' stamps, merges in rank order and
+ * writes the result -- identical on every rank.  All ranks must tick in lockstep with identical inputs; a rank whose
+ * peers stay silent for ~2 s gets QPMPC_ERR_NCCL. */
+#define QPMPC_PEER_BLOB_BYTES 128
+int qpmpc_shard_peer_export(qpmpc_handle *h, unsigned char blob[QPMPC_PEER_BLOB_BYTES]);
+int qpmpc_shard_peer_attach(qpmpc_handle *h, const unsigned char *blobs /* world x QPMPC_PEER_BLOB_BYTES */);
+/* peer exchange if attached (one launch), else partial + ncclAllGather + finish */
+int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
 
 /* ---- device-resident benchmarking helpers (inputs already in HBM; CUDA-event timing on the handle's stream) */
 /* Upload one packet per robot and keep it resident; subsequent qpmpc_bench_resident calls replay it. */

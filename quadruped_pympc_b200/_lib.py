@@ -16,6 +16,7 @@ LIB_DIR = os.path.join(_HERE, 'lib')
 LIB_PATH = os.path.join(LIB_DIR, 'libqpmpc_b200.so')
 HEADER = os.path.join(ROOT, 'include', 'qpmpc.h')
 
+PEER_BLOB_BYTES = 128
 QPMPC_ABI_VERSION = 2
 MAX_HORIZON, MAX_SPLINES, MAX_ELITE = 64, 16, 256
 PARAMETRIZATION = {'zero_order': 0, 'linear_spline': 1, 'cubic_spline': 2}
@@ -70,6 +71,7 @@ EXPORTS = [
     'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
+    'qpmpc_shard_peer_export', 'qpmpc_shard_peer_attach',
     'qpmpc_tick_sharded', 'qpmpc_upload_resident', 'qpmpc_bench_resident', 'qpmpc_fetch_resident_out',
     'qpmpc_kernel_launch_count', 'qpmpc_measure_fp32_peak', 'qpmpc_debug_phase_times',
 ]
@@ -149,6 +151,8 @@ def load():
     lib.qpmpc_shard_get_record.argtypes = [H, _FP]
     lib.qpmpc_nccl_unique_id.argtypes = [C.c_char_p, C.POINTER(C.c_ubyte)]
     lib.qpmpc_shard_init_nccl.argtypes = [H, C.c_char_p, C.POINTER(C.c_ubyte)]
+    lib.qpmpc_shard_peer_export.argtypes = [H, C.POINTER(C.c_ubyte)]
+    lib.qpmpc_shard_peer_attach.argtypes = [H, C.POINTER(C.c_ubyte)]
     lib.qpmpc_tick_sharded.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
     lib.qpmpc_upload_resident.argtypes = [H, C.POINTER(QpmpcTickIn)]
     lib.qpmpc_bench_resident.argtypes = [H, C.c_int, C.c_int, _FP]

@@ -5,6 +5,7 @@
 #include "qpmpc_quad.cuh"
 
 #include <dlfcn.h>
+#include <unistd.h>
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -145,6 +146,11 @@ struct qpmpc_handle {
     int lanes = 1;                    // 1: sample per thread ; 4: four lanes per sample (qpmpc_quad.cuh)
     unsigned long long *d_phase = nullptr;
     KParams partial_kp;               // noise / frequency injection state carried from shard_partial to shard_finish
+    // peer exchange (fused collective of a sample-sharded controller, qpmpc_tick.cuh peer_exchange)
+    float *d_mbox = nullptr;          // this rank's mailbox (cudaMalloc: exportable with cudaIpcGetMemHandle)
+    float *peer_mbox[MAX_PEERS] = {}; // every rank's mailbox as seen from this device
+    bool peer_ipc[MAX_PEERS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
+    bool peer_attached = false;
 };
 
 static size_t round4(size_t x) { return (x + 3) & ~(size_t)3; }
@@ -219,6 +225,9 @@ static void free_handle(qpmpc_handle *h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    for (int w = 0; w < MAX_PEERS; ++w)
+        if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
+    cudaFree(h->d_mbox);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -371,7 +380,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     kp.in = h->kin; kp.out = h->kout; kp.costs = h->d_costs; kp.blk_recs = h->d_blk;
     kp.shard_send = h->d_send; kp.shard_recv = h->d_recv; kp.counters = h->d_counters;
     kp.noise = nullptr; kp.freqs = nullptr;
-    h->direct = (cfg->io_mode == QPMPC_IO_DIRECT && h->R == 1 && W == 1 && kp.in_stride <= PACKET_MAX);
+    h->direct = (cfg->io_mode == QPMPC_IO_DIRECT && h->R == 1 && kp.in_stride <= PACKET_MAX);   // W > 1: peer-exchange ticks only
     if (h->direct) {
         CKH(cudaHostAlloc((void **)&h->h_dout, (kp.out_stride + 4) * sizeof(float), cudaHostAllocMapped));
         memset(h->h_dout, 0, (kp.out_stride + 4) * sizeof(float));
@@ -485,6 +494,31 @@ static int stage_injection(qpmpc_handle *h, const qpmpc_tick_in *in, int count, 
     return QPMPC_OK;
 }
 
+// Direct I/O tick of one controller: the packet travels in kernel-parameter space, the result packet comes back through
+// mapped pinned memory and is detected by its stamp -- no copy-engine hop and no stream synchronisation on the way.
+static inline unsigned int next_seq(qpmpc_handle *h) {
+    if (++h->seq == 0) ++h->seq;                       // 0 is the initial content of every stamp
+    return h->seq;
+}
+static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *out) {
+    memcpy(kp.packet, h->h_in, (size_t)kp.in_stride * sizeof(float));
+    kp.param_packet = 1; kp.host_out = h->d_dout;
+    if (kp.seq == 0) kp.seq = next_seq(h);
+    int rc = launch(h, h->tick_fn, kp, grid);
+    if (rc) return rc;
+    volatile unsigned int *stamp = reinterpret_cast<volatile unsigned int *>(h->h_dout + kp.out_stride);
+    for (unsigned long long spins = 1; *stamp != kp.seq; ++spins) {
+        if ((spins & 0xffff) == 0) {             // a failed launch would never stamp: surface the error instead
+            cudaError_t q = cudaStreamQuery(h->stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) return fail(QPMPC_ERR_CUDA, "tick kernel failed: %s", cudaGetErrorString(q));
+            if (q == cudaSuccess && *stamp != kp.seq) return fail(QPMPC_ERR_CUDA, "tick kernel finished without stamping its result");
+        }
+    }
+    __sync_synchronize();
+    unpack_one(h, 0, h->h_dout, &out[0]);
+    return QPMPC_OK;
+}
+
 static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
     if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
     if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: use qpmpc_tick_sharded / qpmpc_shard_partial");
@@ -498,24 +532,7 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
     const size_t in_bytes = (size_t)R * kp.in_stride * sizeof(float), out_bytes = (size_t)R * kp.out_stride * sizeof(float);
     const dim3 grid(kp.nblk, R);
     const bool mapped = h->cfg.io_mode == QPMPC_IO_MAPPED;
-    if (plain && h->direct) {
-        memcpy(kp.packet, h->h_in, (size_t)kp.in_stride * sizeof(float));
-        kp.param_packet = 1; kp.host_out = h->d_dout; kp.seq = ++h->seq;
-        if (kp.seq == 0) kp.seq = ++h->seq;          // 0 is the initial content of the stamp
-        rc = launch(h, h->tick_fn, kp, grid);
-        if (rc) return rc;
-        volatile unsigned int *stamp = reinterpret_cast<volatile unsigned int *>(h->h_dout + kp.out_stride);
-        for (unsigned long long spins = 1; *stamp != kp.seq; ++spins) {
-            if ((spins & 0xffff) == 0) {             // a failed launch would never stamp: surface the error instead
-                cudaError_t q = cudaStreamQuery(h->stream);
-                if (q != cudaSuccess && q != cudaErrorNotReady) return fail(QPMPC_ERR_CUDA, "tick kernel failed: %s", cudaGetErrorString(q));
-                if (q == cudaSuccess && *stamp != kp.seq) return fail(QPMPC_ERR_CUDA, "tick kernel finished without stamping its result");
-            }
-        }
-        __sync_synchronize();
-        unpack_one(h, 0, h->h_dout, &out[0]);
-        return QPMPC_OK;
-    }
+    if (plain && h->direct) return direct_tick(h, kp, grid, out);
     if (plain && h->cfg.use_graph && !mapped) {
         if (!h->graph_exec) {                      // capture (H2D, kernel, D2H) once; the packet addresses never change
             cudaGraph_t g = nullptr;
@@ -768,10 +785,100 @@ extern "C" int qpmpc_shard_init_nccl(qpmpc_handle *h, const char *libnccl_path, 
     return QPMPC_OK;
 }
 
+// ---- peer exchange: the collective fused into the tick kernel (one launch per tick on every rank) ----
+struct PeerBlob {                         // QPMPC_PEER_BLOB_BYTES = 128
+    cudaIpcMemHandle_t ipc;               // 64 bytes
+    uint64_t pid, raw_ptr;
+    int32_t device, world, rank, rec_stride, robots;
+    unsigned char pad[128 - 64 - 16 - 20];
+};
+static_assert(sizeof(PeerBlob) == QPMPC_PEER_BLOB_BYTES, "peer blob layout");
+
+extern "C" int qpmpc_shard_peer_export(qpmpc_handle *h, unsigned char blob[QPMPC_PEER_BLOB_BYTES]) {
+    if (!h || !blob) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    const int W = h->cfg.shard_world;
+    if (W < 2 || W > MAX_PEERS) return fail(QPMPC_ERR_INVALID, "peer exchange needs 2..%d shards (got %d); use the NCCL path otherwise", MAX_PEERS, W);
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->d_mbox) {
+        const size_t bytes = peer_mbox_bytes(W, h->R, h->kp.shard_rec_stride);
+        CK(cudaMalloc((void **)&h->d_mbox, bytes));
+        CK(cudaMemset(h->d_mbox, 0, bytes));
+        CK(cudaDeviceSynchronize());
+    }
+    PeerBlob b;
+    memset(&b, 0, sizeof(b));
+    CK(cudaIpcGetMemHandle(&b.ipc, h->d_mbox));
+    b.pid = (uint64_t)getpid(); b.raw_ptr = (uint64_t)(uintptr_t)h->d_mbox;
+    b.device = h->cfg.device; b.world = W; b.rank = h->cfg.shard_rank; b.rec_stride = h->kp.shard_rec_stride; b.robots = h->R;
+    memcpy(blob, &b, sizeof(b));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_peer_attach(qpmpc_handle *h, const unsigned char *blobs) {
+    if (!h || !blobs) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h->d_mbox) return fail(QPMPC_ERR_STATE, "qpmpc_shard_peer_export has not been called on this handle");
+    const int W = h->cfg.shard_world, me = h->cfg.shard_rank;
+    CK(cudaSetDevice(h->cfg.device));
+    for (int w = 0; w < W; ++w) {
+        PeerBlob b;
+        memcpy(&b, blobs + (size_t)w * QPMPC_PEER_BLOB_BYTES, sizeof(b));
+        if (b.world != W || b.rank != w || b.rec_stride != h->kp.shard_rec_stride || b.robots != h->R)
+            return fail(QPMPC_ERR_INVALID, "peer blob %d does not describe shard %d of this controller", w, w);
+        if (w == me) { h->peer_mbox[w] = h->d_mbox; continue; }
+        if (b.pid == (uint64_t)getpid()) {              // same process (one host thread per GPU): plain peer access
+            if (b.device != h->cfg.device) {
+                int can = 0;
+                CK(cudaDeviceCanAccessPeer(&can, h->cfg.device, b.device));
+                if (!can) return fail(QPMPC_ERR_CUDA, "device %d cannot access device %d", h->cfg.device, b.device);
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(QPMPC_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+                (void)cudaGetLastError();
+            }
+            h->peer_mbox[w] = (float *)(uintptr_t)b.raw_ptr;
+        } else {
+            void *p = nullptr;
+            CK(cudaIpcOpenMemHandle(&p, b.ipc, cudaIpcMemLazyEnablePeerAccess));
+            h->peer_mbox[w] = (float *)p; h->peer_ipc[w] = true;
+        }
+    }
+    h->peer_attached = true;
+    return QPMPC_OK;
+}
+
+static int tick_peer(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
+    const int R = h->R;
+    for (int r = 0; r < R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
+    KParams kp = h->kp;
+    kp.fused_finish = 0;
+    kp.peer_world = h->cfg.shard_world; kp.peer_rank = h->cfg.shard_rank;
+    memcpy(kp.peer_mbox, h->peer_mbox, sizeof(kp.peer_mbox));
+    kp.seq = next_seq(h);                              // every rank ticks in lockstep: same stamp everywhere
+    int rc = stage_injection(h, in, R, kp);
+    if (rc) return rc;
+    const dim3 grid(kp.nblk, R);
+    const bool plain = (kp.noise_mode == NOISE_PHILOX && !kp.freq_injected);
+    if (plain && h->direct) {
+        rc = direct_tick(h, kp, grid, out);
+        if (rc) return rc;
+    } else {
+        const bool mapped = h->cfg.io_mode == QPMPC_IO_MAPPED;
+        if (!mapped) CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)R * kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        rc = launch(h, h->tick_fn, kp, grid);
+        if (rc) return rc;
+        if (!mapped) CK(cudaMemcpyAsync(h->h_out, h->d_out, (size_t)R * kp.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    }
+    for (int r = 0; r < R; ++r)
+        if (out[r].best_index == -2) return fail(QPMPC_ERR_NCCL, "peer exchange timed out: a shard of this controller did not tick (robot %d)", r);
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
     if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
-    if (!h->comm) return fail(QPMPC_ERR_STATE, "qpmpc_shard_init_nccl has not been called");
+    if (!h->comm && !h->peer_attached) return fail(QPMPC_ERR_STATE, "neither qpmpc_shard_peer_attach nor qpmpc_shard_init_nccl has been called");
     CK(cudaSetDevice(h->cfg.device));
+    if (h->peer_attached) return tick_peer(h, in, out);
     KParams kp;
     int rc = shard_partial_async(h, in, kp);
     if (rc) return rc;

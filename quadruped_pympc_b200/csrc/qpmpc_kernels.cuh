@@ -19,6 +19,7 @@ constexpr int TS = TB + 1;       // tile row stride (floats): bank = (p + t) % 3
 constexpr int MAX_H = 64;
 constexpr int MAX_NS = 16;
 constexpr int MAX_ELITE = 256;
+constexpr int MAX_PEERS = 8;     // ranks of one sample-sharded controller that exchange records through peer memory (one NVSwitch node)
 constexpr int PACKET_MAX = 448;  // floats of one tick packet that may travel in kernel-parameter space (cubic 300, zero-order 396)
 
 enum { ZERO_ORDER = 0, LINEAR = 1, CUBIC = 2 };
@@ -77,6 +78,10 @@ struct KParams {
     unsigned int seq;                       // completion stamp stored after the result packet
     float *host_out;                        // mapped pinned host alias: [out_stride floats][stamp], or NULL
     float packet[PACKET_MAX];
+    // ---- peer exchange of a sample-sharded controller (fused collective, qpmpc_tick.cuh peer_exchange) ----
+    int peer_world;                         // > 1: the last block pushes its shard record into every peer's mailbox over
+    int peer_rank;                          //      NVLink, waits for the peers' records and finishes in the same launch
+    float *peer_mbox[MAX_PEERS];            // mailbox base of every rank (own entry = local memory): see peer_exchange
     unsigned long long *phase_ns;           // debug (qpmpc_debug_phase_times): %globaltimer at phase boundaries, or NULL
 };
 

@@ -298,12 +298,7 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     float M, S; int IDX;
     shard_reduce<METHOD, QTB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 9);
-    if (kp.fused_finish) {
-        __threadfence();
-        __syncthreads();
-        finish<PARAM, ADAPTIVE, METHOD, QTB>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
-        publish_to_host(kp, r);
-    }
+    after_shard_reduce<PARAM, ADAPTIVE, METHOD, QTB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 11);
     if (t == 0) kp.counters[r] = 0u;
 }

@@ -347,6 +347,92 @@ __device__ __forceinline__ void publish_to_host(const KParams &kp, int r) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Fused collective of a sample-sharded controller (one exchange step per tick): instead of a separate
+// all-gather launch, the last block of each shard stores its record straight into every peer GPU's mailbox (plain
+// stores to peer memory: NVLink / NVSwitch), publishes a sequence stamp with system-scope release, and spins
+// (acquire) until all `world` stamps of this tick have arrived in its own mailbox; finish() then merges the records
+// in rank order -- every rank ends the same launch with the same control.
+//   mailbox of one rank: recs [2 parity][world][R][shard_rec_stride] floats, then stamps [2][world][R] u32.
+//   Two parities: a rank that is one tick ahead writes the other half, and cannot get two ticks ahead because it
+//   needs this rank's record of the tick in between.
+// Returns false if a peer's stamp did not arrive within ~2 s (peer process gone): the caller reports it.
+// ------------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t peer_mbox_rec_floats(int world, int R, int stride) { return (size_t)2 * world * R * stride; }
+__host__ __device__ inline size_t peer_mbox_bytes(int world, int R, int stride) {
+    return peer_mbox_rec_floats(world, R, stride) * sizeof(float) + (size_t)2 * world * R * sizeof(unsigned int);
+}
+
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <int NT>
+__device__ bool peer_exchange(const KParams &kp, int r, const float *&recs, size_t &rec_stride) {
+    const int W = kp.peer_world, R = gridDim.y, stride = kp.shard_rec_stride, t = threadIdx.x;
+    const unsigned int par = kp.seq & 1u;
+    const size_t slot = ((size_t)(par * W + kp.peer_rank) * R + r);          // [parity][my rank][robot]
+    const float *mine = kp.shard_send + (size_t)r * stride;                   // written by this block in shard_reduce
+    __syncthreads();
+    // 1. push the record: float4 stores, one peer after the other per thread (W * stride/4 <= a few hundred stores)
+    const int n4 = stride >> 2;
+    for (int e = t; e < W * n4; e += NT) {
+        const int w = e / n4, k = e - w * n4;
+        reinterpret_cast<float4 *>(kp.peer_mbox[w] + slot * stride)[k] = reinterpret_cast<const float4 *>(mine)[k];
+    }
+    __threadfence_system();
+    __syncthreads();
+    // 2. stamp every peer's mailbox (release: the record is visible before the stamp)
+    const size_t stamps_off = peer_mbox_rec_floats(W, R, stride);
+    if (t < W) st_release_sys(reinterpret_cast<unsigned int *>(kp.peer_mbox[t] + stamps_off) + slot, kp.seq);
+    // 3. wait for the W stamps of this tick in the local mailbox
+    __shared__ int s_ok;
+    if (t == 0) s_ok = 1;
+    __syncthreads();
+    float *local = kp.peer_mbox[kp.peer_rank];
+    if (t < W) {
+        const unsigned int *st = reinterpret_cast<const unsigned int *>(local + stamps_off) + ((size_t)(par * W + t) * R + r);
+        unsigned long long t0, now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (ld_acquire_sys(st) != kp.seq) {
+            __nanosleep(40);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (now - t0 > 2000000000ull) { s_ok = 0; break; }
+        }
+    }
+    __syncthreads();
+    recs = local + ((size_t)par * W * R + r) * stride;
+    rec_stride = (size_t)R * stride;
+    return s_ok != 0;
+}
+
+// what the tick kernels do after shard_reduce: finish locally (one shard), exchange with the peers and finish, or stop
+// (records go to a separate collective + finish_kernel).  BESTIDX = -2 flags a peer time-out to the host.
+template <int PARAM, bool ADAPTIVE, int METHOD, int NT>
+__device__ __forceinline__ void after_shard_reduce(const KParams &kp, int r, const Smem &s, float M, int IDX, float S) {
+    if (kp.fused_finish) {
+        __threadfence();
+        __syncthreads();
+        finish<PARAM, ADAPTIVE, METHOD, NT>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
+        publish_to_host(kp, r);
+    } else if (kp.peer_world > 1) {
+        const float *recs;
+        size_t rec_stride;
+        const bool ok = peer_exchange<NT>(kp, r, recs, rec_stride);
+        finish<PARAM, ADAPTIVE, METHOD, NT>(kp, r, s, recs, kp.peer_world, rec_stride);
+        if (!ok) {
+            __syncthreads();
+            if (threadIdx.x == 0) (kp.out + (size_t)r * kp.out_stride)[OUT_BESTIDX] = __int_as_float(-2);
+        }
+        publish_to_host(kp, r);
+    }
+}
+
 // ======================================================================================================
 // The tick kernel.  grid = (nblk, R), block = TB.  dynamic smem = smem_floats(...) * 4 bytes.
 // ======================================================================================================
@@ -454,12 +540,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
     float M, S; int IDX;
     shard_reduce<METHOD, TB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 9);
-    if (kp.fused_finish) {
-        __threadfence();
-        __syncthreads();
-        finish<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
-        publish_to_host(kp, r);
-    }
+    after_shard_reduce<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 11);
     if (t == 0) kp.counters[r] = 0u;
 }

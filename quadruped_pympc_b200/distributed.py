@@ -32,14 +32,33 @@ def broadcast_bytes(payload: bytes | None, nbytes: int, src: int = 0) -> bytes:
     return bytes(t.cpu().numpy().tobytes())
 
 
-def make_sharded_controller(cfg, rank: int | None = None, world: int | None = None):
-    """`Sampling_MPC` owning shard `rank` of `world`, NCCL communicator initialised (ranks from torch.distributed)."""
+def all_gather_bytes(payload: bytes) -> list:
+    """Every rank contributes `payload` (same length everywhere); returns the payloads in rank order."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return [payload]
+    dev = 'cuda' if dist.get_backend() == 'nccl' else 'cpu'
+    mine = torch.frombuffer(bytearray(payload), dtype=torch.uint8).to(dev)
+    parts = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(parts, mine)
+    return [bytes(p.cpu().numpy().tobytes()) for p in parts]
+
+
+def make_sharded_controller(cfg, rank: int | None = None, world: int | None = None, exchange: str = 'peer'):
+    """`Sampling_MPC` owning shard `rank` of `world` (ranks from torch.distributed).
+    exchange = 'peer': the record exchange is fused into the tick kernel over NVLink peer memory (2..8 ranks of one
+    node, one launch per tick); 'nccl': partial kernel + ncclAllGather + finish kernel."""
     import torch.distributed as dist
     from .sampling_mpc import Sampling_MPC
     rank = dist.get_rank() if rank is None else rank
     world = dist.get_world_size() if world is None else world
+    if exchange not in ('peer', 'nccl'):
+        raise ValueError(f'unknown exchange {exchange!r}')
     ctrl = Sampling_MPC(cfg, shard_rank=rank, shard_world=world)
-    if world > 1:
+    if world > 1 and exchange == 'peer':
+        ctrl.peer_attach(all_gather_bytes(ctrl.peer_export()))
+    elif world > 1:
         uid = Sampling_MPC.nccl_unique_id() if rank == 0 else None
         ctrl.init_nccl(broadcast_bytes(uid, 128, 0))
     return ctrl

@@ -242,6 +242,23 @@ class Sampling_MPC:
         _lib.check(_lib.load().qpmpc_shard_init_nccl(self._ensure(), _lib.find_libnccl().encode(), buf))
         return self
 
+    def peer_export(self) -> bytes:
+        """128-byte description of this shard's mailbox (CUDA IPC handle); all-gather the blobs of every rank (e.g.
+        `distributed.all_gather_bytes`) and hand them to `peer_attach` in rank order."""
+        buf = (C.c_ubyte * _lib.PEER_BLOB_BYTES)()
+        _lib.check(_lib.load().qpmpc_shard_peer_export(self._ensure(), buf))
+        return bytes(buf)
+
+    def peer_attach(self, blobs):
+        """Open every rank's mailbox: from now on a sharded tick is ONE launch per rank with the record exchange fused
+        into the kernel (stores over NVLink peer memory) instead of partial + ncclAllGather + finish."""
+        blobs = list(blobs)
+        if len(blobs) != self._shard[1] or any(len(b) != _lib.PEER_BLOB_BYTES for b in blobs):
+            raise _lib.QpmpcError(_lib.ERR_INVALID, f'need {self._shard[1]} blobs of {_lib.PEER_BLOB_BYTES} bytes')
+        buf = (C.c_ubyte * (len(blobs) * _lib.PEER_BLOB_BYTES)).from_buffer_copy(b''.join(blobs))
+        _lib.check(_lib.load().qpmpc_shard_peer_attach(self._ensure(), buf))
+        return self
+
     def shard_partial(self, state, reference, contact_sequence, best, key, sigma=None, timing=None, nominal=None,
                       optimize_swing=None, noise=None, step_freqs=None) -> np.ndarray:
         """Rollouts + local reduction of this shard's slice; returns the shard record (floats) for a caller-side gather
