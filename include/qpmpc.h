@@ -178,6 +178,11 @@ int qpmpc_shard_init_nccl(qpmpc_handle *h, const char *libnccl_path, const unsig
 #define QPMPC_PEER_BLOB_BYTES 128
 int qpmpc_shard_peer_export(qpmpc_handle *h, unsigned char blob[QPMPC_PEER_BLOB_BYTES]);
 int qpmpc_shard_peer_attach(qpmpc_handle *h, const unsigned char *blobs /* world x QPMPC_PEER_BLOB_BYTES */);
+/* Test hooks: cover the fused exchange on ONE GPU without two kernels waiting on each other.  loopback: absent peers
+ * are a sink on this device.  inject: play peer `rank` from the host before the tick is launched (its record and the
+ * stamp of the upcoming tick go into the local mailbox). */
+int qpmpc_shard_peer_loopback(qpmpc_handle *h);
+int qpmpc_shard_peer_inject(qpmpc_handle *h, int rank, const float *host_rec);
 /* peer exchange if attached (one launch), else partial + ncclAllGather + finish */
 int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
 

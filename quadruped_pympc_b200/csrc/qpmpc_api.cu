@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -129,7 +130,7 @@ struct qpmpc_handle {
     cudaStream_t stream = nullptr;
     float *d_in = nullptr, *d_out = nullptr, *d_costs = nullptr, *d_blk = nullptr, *d_send = nullptr, *d_recv = nullptr;
     float *d_noise = nullptr, *d_freqs = nullptr, *d_flush = nullptr, *d_sigma = nullptr;
-    unsigned int *d_counters = nullptr;
+    unsigned int *d_counters = nullptr, *d_cem_hist = nullptr;
     float *h_in = nullptr, *h_out = nullptr, *h_rec = nullptr;   // pinned (mapped when io_mode == MAPPED)
     float *kin = nullptr, *kout = nullptr;                       // what the kernel dereferences for in / out
     size_t noise_capacity = 0, freqs_capacity = 0;
@@ -148,6 +149,7 @@ struct qpmpc_handle {
     KParams partial_kp;               // noise / frequency injection state carried from shard_partial to shard_finish
     // peer exchange (fused collective of a sample-sharded controller, qpmpc_tick.cuh peer_exchange)
     float *d_mbox = nullptr;          // this rank's mailbox (cudaMalloc: exportable with cudaIpcGetMemHandle)
+    float *d_sink = nullptr;          // loopback test hook: where the records pushed to absent peers go
     float *peer_mbox[MAX_PEERS] = {}; // every rank's mailbox as seen from this device
     bool peer_ipc[MAX_PEERS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
     bool peer_attached = false;
@@ -227,12 +229,12 @@ static void free_handle(qpmpc_handle *h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
-    cudaFree(h->d_mbox);
+    cudaFree(h->d_mbox); cudaFree(h->d_sink);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     cudaFree(h->d_in); cudaFree(h->d_out); cudaFree(h->d_costs); cudaFree(h->d_blk); cudaFree(h->d_send); cudaFree(h->d_recv);
-    cudaFree(h->d_noise); cudaFree(h->d_freqs); cudaFree(h->d_flush); cudaFree(h->d_counters); cudaFree(h->d_sigma); cudaFree(h->d_phase);
+    cudaFree(h->d_noise); cudaFree(h->d_freqs); cudaFree(h->d_flush); cudaFree(h->d_counters); cudaFree(h->d_cem_hist); cudaFree(h->d_sigma); cudaFree(h->d_phase);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->h_rec) cudaFreeHost(h->h_rec);
@@ -369,6 +371,10 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
     CKH(cudaMalloc((void **)&h->d_sigma, (size_t)h->P * sizeof(float)));
     CKH(cudaMemset(h->d_counters, 0, R * sizeof(unsigned int)));
+    if (cfg->method == QPMPC_CEM_MPPI) {       // per-robot cost histogram: zero between ticks (the last block re-zeroes it)
+        CKH(cudaMalloc((void **)&h->d_cem_hist, R * (size_t)CEM_BINS * sizeof(unsigned int)));
+        CKH(cudaMemset(h->d_cem_hist, 0, R * (size_t)CEM_BINS * sizeof(unsigned int)));
+    }
     CKH(cudaMemset(h->d_in, 0, R * kp.in_stride * sizeof(float)));
     CKH(cudaMemset(h->d_out, 0, R * kp.out_stride * sizeof(float)));
     if (cfg->io_mode == QPMPC_IO_MAPPED) {
@@ -378,7 +384,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
         h->kin = h->d_in; h->kout = h->d_out;
     }
     kp.in = h->kin; kp.out = h->kout; kp.costs = h->d_costs; kp.blk_recs = h->d_blk;
-    kp.shard_send = h->d_send; kp.shard_recv = h->d_recv; kp.counters = h->d_counters;
+    kp.shard_send = h->d_send; kp.shard_recv = h->d_recv; kp.counters = h->d_counters; kp.cem_hist = h->d_cem_hist;
     kp.noise = nullptr; kp.freqs = nullptr;
     h->direct = (cfg->io_mode == QPMPC_IO_DIRECT && h->R == 1 && kp.in_stride <= PACKET_MAX);   // W > 1: peer-exchange ticks only
     if (h->direct) {
@@ -790,7 +796,8 @@ struct PeerBlob {                         // QPMPC_PEER_BLOB_BYTES = 128
     cudaIpcMemHandle_t ipc;               // 64 bytes
     uint64_t pid, raw_ptr;
     int32_t device, world, rank, rec_stride, robots;
-    unsigned char pad[128 - 64 - 16 - 20];
+    unsigned char uuid[16];               // physical GPU: two shards of one controller may not share a GPU (see attach)
+    unsigned char pad[128 - 64 - 16 - 20 - 16];
 };
 static_assert(sizeof(PeerBlob) == QPMPC_PEER_BLOB_BYTES, "peer blob layout");
 
@@ -807,6 +814,9 @@ extern "C" int qpmpc_shard_peer_export(qpmpc_handle *h, unsigned char blob[QPMPC
     }
     PeerBlob b;
     memset(&b, 0, sizeof(b));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, h->cfg.device));
+    memcpy(b.uuid, &prop.uuid, 16);
     CK(cudaIpcGetMemHandle(&b.ipc, h->d_mbox));
     b.pid = (uint64_t)getpid(); b.raw_ptr = (uint64_t)(uintptr_t)h->d_mbox;
     b.device = h->cfg.device; b.world = W; b.rank = h->cfg.shard_rank; b.rec_stride = h->kp.shard_rec_stride; b.robots = h->R;
@@ -819,6 +829,13 @@ extern "C" int qpmpc_shard_peer_attach(qpmpc_handle *h, const unsigned char *blo
     if (!h->d_mbox) return fail(QPMPC_ERR_STATE, "qpmpc_shard_peer_export has not been called on this handle");
     const int W = h->cfg.shard_world, me = h->cfg.shard_rank;
     CK(cudaSetDevice(h->cfg.device));
+    // Every shard's kernel waits for its peers' stamps, so the W kernels must be able to run at the same time: one
+    // physical GPU per shard.  (Two waiting kernels on one GPU are not guaranteed to be co-scheduled.)
+    for (int a = 0; a < W; ++a)
+        for (int b = a + 1; b < W; ++b)
+            if (memcmp(blobs + (size_t)a * QPMPC_PEER_BLOB_BYTES + offsetof(PeerBlob, uuid),
+                       blobs + (size_t)b * QPMPC_PEER_BLOB_BYTES + offsetof(PeerBlob, uuid), 16) == 0)
+                return fail(QPMPC_ERR_INVALID, "shards %d and %d are on the same GPU: the peer exchange needs one GPU per shard", a, b);
     for (int w = 0; w < W; ++w) {
         PeerBlob b;
         memcpy(&b, blobs + (size_t)w * QPMPC_PEER_BLOB_BYTES, sizeof(b));
@@ -842,6 +859,39 @@ extern "C" int qpmpc_shard_peer_attach(qpmpc_handle *h, const unsigned char *blo
         }
     }
     h->peer_attached = true;
+    return QPMPC_OK;
+}
+
+// Test hooks (single-GPU coverage of peer_exchange without two kernels waiting on each other): `loopback` points every
+// absent peer at a sink on this device; `inject` plays a peer's part from the host BEFORE the tick is launched -- it
+// writes that peer's record and the stamp of the upcoming tick into the local mailbox.
+extern "C" int qpmpc_shard_peer_loopback(qpmpc_handle *h) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    const int W = h->cfg.shard_world;
+    if (W < 2 || W > MAX_PEERS) return fail(QPMPC_ERR_INVALID, "peer exchange needs 2..%d shards (got %d)", MAX_PEERS, W);
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t bytes = peer_mbox_bytes(W, h->R, h->kp.shard_rec_stride);
+    if (!h->d_mbox) { CK(cudaMalloc((void **)&h->d_mbox, bytes)); CK(cudaMemset(h->d_mbox, 0, bytes)); }
+    if (!h->d_sink) { CK(cudaMalloc((void **)&h->d_sink, bytes)); CK(cudaMemset(h->d_sink, 0, bytes)); }
+    CK(cudaDeviceSynchronize());
+    for (int w = 0; w < W; ++w) h->peer_mbox[w] = (w == h->cfg.shard_rank) ? h->d_mbox : h->d_sink;
+    h->peer_attached = true;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_peer_inject(qpmpc_handle *h, int rank, const float *host_rec) {
+    if (!h || !host_rec) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    const int W = h->cfg.shard_world, R = h->R, stride = h->kp.shard_rec_stride;
+    if (!h->d_mbox || rank < 0 || rank >= W || rank == h->cfg.shard_rank) return fail(QPMPC_ERR_INVALID, "bad rank / no mailbox");
+    CK(cudaSetDevice(h->cfg.device));
+    unsigned int seq = h->seq + 1u;
+    if (seq == 0u) seq = 1u;
+    const unsigned int par = seq & 1u;
+    const size_t slot = (size_t)(par * W + rank) * R;
+    CK(cudaMemcpy(h->d_mbox + slot * stride, host_rec, (size_t)R * stride * sizeof(float), cudaMemcpyHostToDevice));
+    std::vector<unsigned int> stamps((size_t)R, seq);
+    unsigned int *d_stamps = reinterpret_cast<unsigned int *>(h->d_mbox + peer_mbox_rec_floats(W, R, stride)) + slot;
+    CK(cudaMemcpy(d_stamps, stamps.data(), (size_t)R * sizeof(unsigned int), cudaMemcpyHostToDevice));
     return QPMPC_OK;
 }
 

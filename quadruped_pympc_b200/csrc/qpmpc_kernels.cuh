@@ -19,6 +19,9 @@ constexpr int TS = TB + 1;       // tile row stride (floats): bank = (p + t) % 3
 constexpr int MAX_H = 64;
 constexpr int MAX_NS = 16;
 constexpr int MAX_ELITE = 256;
+constexpr int CEM_SHIFT = 20;    // first-level digit of the elite selection: sign + exponent + 3 mantissa bits of the cost
+constexpr int CEM_BINS = 4096;
+constexpr int CEM_CAND = 2048 - MAX_ELITE;   // candidate keys (threshold bin) held in shared memory during the refinement
 constexpr int MAX_PEERS = 8;     // ranks of one sample-sharded controller that exchange records through peer memory (one NVSwitch node)
 constexpr int PACKET_MAX = 448;  // floats of one tick packet that may travel in kernel-parameter space (cubic 300, zero-order 396)
 
@@ -71,6 +74,7 @@ struct KParams {
     float *shard_send;                      // [R][shard_rec_stride]  (this shard's record)
     const float *shard_recv;                // [world][R][shard_rec_stride]
     unsigned int *counters;                 // [R]
+    unsigned int *cem_hist;                 // [R][CEM_BINS] histogram of the cost bits >> CEM_SHIFT, filled by every sample (CEM only)
     const float *noise;                     // injected: [R][N][P] (additional noise, or explicit params in MODE_ROLLOUT)
     const float *freqs;                     // injected: [R][N]
     // ---- direct I/O (one controller, host buffers): no copy-engine hops around the kernel ----
@@ -606,6 +610,235 @@ static __device__ void block_topk(const float *costs, int n, int idx_base, int k
     for (int size = 2; size <= MAX_ELITE; size <<= 1) {
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
             for (int i = t; i < MAX_ELITE / 2; i += TB) {
+                const int lo = 2 * i - (i & (stride - 1));
+                const int hi = lo + stride;
+                const bool up = ((lo & size) == 0);
+                const unsigned long long a = s_keys[lo], b = s_keys[hi];
+                if ((a > b) == up) { s_keys[lo] = b; s_keys[hi] = a; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Exact top-k by (cost, index), histogram-assisted (the CEM elite selection of one shard, S:1075 | A:1115).
+// Every sample has already counted itself into g_hist[cost bits >> CEM_SHIFT] (warp-aggregated REDs in the rollout
+// phase, cem_count_cost), so the last block starts with the first radix level for free:
+//   1. scan the 4096 bins (each thread owns CEM_BINS / NT consecutive bins) -> threshold bin b*, #keys below it; zero
+//      the bins for the next tick;
+//   1b. only if b* holds more keys than the shared-memory candidate list (cost distributions narrower than 1/8 octave):
+//      one pass over the costs builds a second 4096-bin histogram of the next 12 cost bits inside b* (shared memory);
+//   2. ONE pass over the costs (8 independent loads in flight per thread): prefix < threshold -> selected, prefix ==
+//      threshold -> candidate list in shared memory;
+//   3. radix-select the remaining (k - below) among the candidates in shared memory, 8-bit digits over the low key
+//      bits, warp-parallel bin scan, early exit as soon as a bucket is taken whole (costs are nearly always distinct,
+//      so this ends inside the remaining cost bits);
+//   4. bitonic sort of the k winners.
+// Falls back to block_topk (8 passes over global memory) if even the 24-bit prefix leaves more than CEM_CAND candidates
+// (thousands of bit-identical costs).  Same contract as block_topk; s_keys: >= MAX_ELITE + CEM_CAND u64.
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cem_count_cost(unsigned int *g_hist, float cost) {
+    const unsigned int bin = __float_as_uint(cost) >> CEM_SHIFT;
+    const unsigned int peers = __match_any_sync(__activemask(), bin);           // one RED per distinct bin per warp
+    if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(g_hist + bin, (unsigned int)__popc(peers));
+}
+
+// Block-wide search of the bin where the running count reaches `need`; bins[] are read through LOAD(i), i in
+// [0, CEM_BINS).  Result in s_misc[0..2] = (bin | 0xffffffff, count below, count inside).  s_warp: >= NT/32 u32.
+template <int NT, class LOAD>
+__device__ __forceinline__ void cem_find_bin(LOAD load, unsigned int need, unsigned int *s_warp, unsigned int *s_misc) {
+    constexpr int BPT = CEM_BINS / NT;
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    unsigned int mysum = 0u;
+#pragma unroll 8
+    for (int j = 0; j < BPT; ++j) mysum += load(t * BPT + ((j + t) & (BPT - 1)));   // rotated: conflict-free in shared memory
+    unsigned int incl = mysum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    __syncthreads();
+    if (lane == 31) s_warp[wid] = incl;
+    if (t == 0) s_misc[0] = 0xffffffffu;
+    __syncthreads();
+    unsigned int excl = incl - mysum;
+    for (int w = 0; w < wid; ++w) excl += s_warp[w];
+    if (excl < need && excl + mysum >= need) {                                    // exactly one thread
+        unsigned int acc = excl;
+        for (int j = 0; j < BPT; ++j) {
+            const unsigned int c = load(t * BPT + j);
+            if (acc + c >= need) { s_misc[0] = (unsigned int)(t * BPT + j); s_misc[1] = acc; s_misc[2] = c; break; }
+            acc += c;
+        }
+    }
+    __syncthreads();
+}
+
+// Visit every cost of one shard from a single block with many loads in flight: 8 x 16-byte loads per thread when the
+// slice is 16-byte aligned (32 costs per thread per round), scalar loads otherwise.  f(cost bits, local index).
+template <int NT, class F>
+__device__ __forceinline__ void cem_for_each_cost(const float *costs, int n, F f) {
+    const int t = threadIdx.x;
+    if ((reinterpret_cast<uintptr_t>(costs) & 15) == 0) {
+        const int n4 = n >> 2;
+        const uint4 *c4 = reinterpret_cast<const uint4 *>(costs);
+        for (int base = 0; base < n4; base += 8 * NT) {
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = base + u * NT + t;
+                v[u] = i < n4 ? __ldcg(c4 + i) : make_uint4(~0u, ~0u, ~0u, ~0u);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = base + u * NT + t;
+                if (i < n4) { f(v[u].x, 4 * i); f(v[u].y, 4 * i + 1); f(v[u].z, 4 * i + 2); f(v[u].w, 4 * i + 3); }
+            }
+        }
+        for (int i = (n4 << 2) + t; i < n; i += NT) f(__float_as_uint(__ldcg(costs + i)), i);
+        return;
+    }
+    for (int base = 0; base < n; base += 8 * NT) {
+        unsigned int cb[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int i = base + u * NT + t;
+            cb[u] = i < n ? __float_as_uint(__ldcg(costs + i)) : ~0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int i = base + u * NT + t;
+            if (i < n) f(cb[u], i);
+        }
+    }
+}
+
+template <int NT>
+static __device__ void block_topk_hist(const float *costs, int n, int idx_base, int k, unsigned int *g_hist,
+                                       unsigned long long *s_keys, unsigned int *s_hist, unsigned int *s_misc) {
+    static_assert((CEM_BINS / NT) >= 4 && ((CEM_BINS / NT) & (CEM_BINS / NT - 1)) == 0, "bins per thread: power of two");
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    // ---- 1. threshold bin of the first 12 key bits ----
+    {   // stage the global histogram in shared memory (coalesced 16-byte loads), leave it zeroed for the next tick
+        uint4 *s4 = reinterpret_cast<uint4 *>(s_keys);
+        uint4 *g4 = reinterpret_cast<uint4 *>(g_hist);
+        for (int i = t; i < CEM_BINS / 4; i += NT) { s4[i] = __ldcg(g4 + i); g4[i] = make_uint4(0u, 0u, 0u, 0u); }
+        __syncthreads();
+    }
+    {
+        const unsigned int *s_h1 = reinterpret_cast<const unsigned int *>(s_keys);
+        cem_find_bin<NT>([&](int i) { return s_h1[i]; }, (unsigned int)k, s_hist, s_misc);
+    }
+    unsigned int thr_prefix = s_misc[0], below = s_misc[1], m = s_misc[2];
+    int pshift = CEM_SHIFT;                           // the prefix is cost bits >> pshift
+    __syncthreads();
+    if (thr_prefix != 0xffffffffu && m > (unsigned int)CEM_CAND) {
+        // ---- 1b. second level inside the threshold bin: cost bits [CEM_SHIFT-1 : CEM_SHIFT-12] ----
+        unsigned int *s_h2 = reinterpret_cast<unsigned int *>(s_keys);            // 4096 u32 = the first 2048 u64 slots
+        for (int i = t; i < CEM_BINS; i += NT) s_h2[i] = 0u;
+        __syncthreads();
+        {
+            const unsigned int bin1 = thr_prefix;
+            cem_for_each_cost<NT>(costs, n, [&](unsigned int cb, int) {
+                if ((cb >> CEM_SHIFT) == bin1) atomicAdd(&s_h2[(cb >> (CEM_SHIFT - 12)) & (CEM_BINS - 1)], 1u);
+            });
+        }
+        __syncthreads();
+        const unsigned int bin1 = thr_prefix, below1 = below;
+        cem_find_bin<NT>([&](int i) { return s_h2[i]; }, (unsigned int)k - below1, s_hist, s_misc);
+        thr_prefix = s_misc[0] == 0xffffffffu ? 0xffffffffu : ((bin1 << 12) | s_misc[0]);
+        below = below1 + s_misc[1]; m = s_misc[2];
+        pshift = CEM_SHIFT - 12;
+        __syncthreads();
+    }
+    if (thr_prefix == 0xffffffffu || m > (unsigned int)CEM_CAND) {                 // histogram unusable: exact slow path
+        block_topk<NT>(costs, n, idx_base, k, s_keys, s_hist, s_misc);
+        return;
+    }
+    if (t == 0) { s_misc[3] = 0u; s_misc[4] = 0u; }
+    __syncthreads();
+    unsigned long long *s_cand = s_keys + MAX_ELITE;
+    // ---- 2. one pass over the costs ----
+    cem_for_each_cost<NT>(costs, n, [&](unsigned int cb, int i) {
+        const unsigned int b = cb >> pshift;
+        if (b <= thr_prefix) {
+            const unsigned long long key = ((unsigned long long)cb << 32) | (unsigned int)(idx_base + i);
+            if (b < thr_prefix) { const unsigned int slot = atomicAdd(&s_misc[3], 1u); if (slot < MAX_ELITE) s_keys[slot] = key; }
+            else { const unsigned int slot = atomicAdd(&s_misc[4], 1u); if (slot < CEM_CAND) s_cand[slot] = key; }
+        }
+    });
+    __syncthreads();
+    // ---- 3. refine inside the threshold prefix: radix select over the low (32 + pshift) key bits ----
+    const int low_bits = 32 + pshift;
+    const unsigned long long low_mask = ~(~0ull << low_bits);
+    int need = k - (int)below;                        // 1 <= need <= m
+    unsigned long long thr_low = low_mask;            // candidates with (key & low_mask) <= thr_low are selected
+    if ((unsigned int)need < m) {
+        unsigned long long prefix = 0ull, above = 0ull;   // decided low bits
+        for (int shift = low_bits - 8; ; shift -= 8) {
+            const int sh = shift < 0 ? 0 : shift;
+            const int width = shift < 0 ? 8 + shift : 8;
+            const unsigned int dmask = (1u << width) - 1u;
+            for (int b = t; b < 256; b += NT) s_hist[b] = 0u;
+            __syncthreads();
+            for (unsigned int c = t; c < m; c += NT) {
+                const unsigned long long key = s_cand[c];
+                if ((key & above) == prefix) atomicAdd(&s_hist[(unsigned int)(key >> sh) & dmask], 1u);
+            }
+            __syncthreads();
+            if (wid == 0) {                           // 256 bins: 8 per lane, warp scan
+                unsigned int h8[8], sum = 0u;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { h8[j] = s_hist[lane * 8 + j]; sum += h8[j]; }
+                unsigned int inc = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned int v = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += v;
+                }
+                const unsigned int ex = inc - sum;
+                if (ex < (unsigned int)need && ex + sum >= (unsigned int)need) {
+                    unsigned int acc = ex;
+                    int d = -1;
+                    unsigned int accd = 0u, cntd = 0u;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (d < 0 && acc + h8[j] >= (unsigned int)need) { d = lane * 8 + j; accd = acc; cntd = h8[j]; }
+                        acc += h8[j];
+                    }
+                    s_misc[5] = (unsigned int)d; s_misc[6] = accd; s_misc[7] = cntd;
+                }
+            }
+            __syncthreads();
+            const unsigned int d = s_misc[5], accd = s_misc[6], cntd = s_misc[7];
+            prefix |= (unsigned long long)d << sh;
+            above |= (unsigned long long)dmask << sh;
+            need -= (int)accd;
+            __syncthreads();
+            if ((unsigned int)need == cntd || sh == 0) {          // the bucket is taken whole (always true at the last digit)
+                thr_low = prefix | (low_mask & ~above);
+                break;
+            }
+        }
+    }
+    for (unsigned int c = t; c < m; c += NT) {
+        const unsigned long long key = s_cand[c];
+        if ((key & low_mask) <= thr_low) {
+            const unsigned int slot = atomicAdd(&s_misc[3], 1u);
+            if (slot < MAX_ELITE) s_keys[slot] = key;
+        }
+    }
+    __syncthreads();
+    const unsigned int got = s_misc[3];               // == k
+    __syncthreads();
+    for (int i = (int)got + t; i < MAX_ELITE; i += NT) s_keys[i] = ~0ull;
+    __syncthreads();
+    // ---- 4. sort the winners ----
+    for (int size = 2; size <= MAX_ELITE; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int i = t; i < MAX_ELITE / 2; i += NT) {
                 const int lo = 2 * i - (i & (stride - 1));
                 const int hi = lo + stride;
                 const bool up = ((lo & size) == 0);

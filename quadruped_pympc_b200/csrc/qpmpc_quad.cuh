@@ -251,7 +251,11 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             if (kp.mode == MODE_TICK) {                          // NaN / +-Inf -> 1e6, S:686-687
                 if (isnan(cost) || isinf(cost)) cost = 1000000.0f;
             }
-            if (leg == 0) kp.costs[(size_t)r * kp.n_local + local] = cost;
+            if (leg == 0) {
+                kp.costs[(size_t)r * kp.n_local + local] = cost;
+                if (METHOD == CEM_MPPI && kp.mode == MODE_TICK)  // first radix level of the elite selection (block_topk_hist)
+                    cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, cost);
+            }
         }
         if (blk == 0 && it == 0) phase_mark(kp, 3);
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }

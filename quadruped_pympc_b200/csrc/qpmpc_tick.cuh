@@ -188,7 +188,8 @@ __device__ void shard_reduce(const KParams &kp, int r, const Smem &s, float &M, 
         unsigned int *hist = reinterpret_cast<unsigned int *>(s.tile + 2 * SCRATCH_KEYS);
         unsigned int *misc = hist + 256;
         const int k = kp.elite_k < kp.n_local ? kp.elite_k : kp.n_local;
-        block_topk<NT>(kp.costs + (size_t)r * kp.n_local, kp.n_local, kp.sample_base, k, keys, hist, misc);
+        block_topk_hist<NT>(kp.costs + (size_t)r * kp.n_local, kp.n_local, kp.sample_base, k, kp.cem_hist + (size_t)r * CEM_BINS,
+                            keys, hist, misc);
         for (int j = t; j < kp.elite_k; j += TB) {
             const unsigned long long key = j < k ? keys[j] : ~0ull;
             rec[REC_V + kp.P + 2 * j] = __uint_as_float((unsigned int)(key >> 32));
@@ -292,7 +293,8 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
                 const float *row = kp.noise + ((size_t)r * kp.N + my_idx) * kp.P;
                 for (int p = 0; p < kp.P; ++p) tcol[p * TS] = __ldg(row + p);
             } else {
-                for (int q = 0; q < kp.P / 4; ++q) {
+#pragma unroll 4
+                for (int q = 0; q < kp.P / 4; ++q) {                // independent Philox chains: unrolled for ILP (4 warps alone on the SM)
                     const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, my_idx, q, s_sigma);
                     tcol[(4 * q) * TS] = e.x; tcol[(4 * q + 1) * TS] = e.y; tcol[(4 * q + 2) * TS] = e.z; tcol[(4 * q + 3) * TS] = e.w;
                 }
@@ -491,6 +493,8 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
                 if (isnan(cost) || isinf(cost)) cost = 1000000.0f;
             }
             kp.costs[(size_t)r * kp.n_local + local] = cost;
+            if (METHOD == CEM_MPPI && kp.mode == MODE_TICK)      // first radix level of the elite selection (block_topk_hist)
+                cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, cost);
         }
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }
         if (blk == 0 && it == 0) phase_mark(kp, 3);

@@ -259,6 +259,16 @@ class Sampling_MPC:
         _lib.check(_lib.load().qpmpc_shard_peer_attach(self._ensure(), buf))
         return self
 
+    def peer_loopback(self):
+        """Test hook: run the fused exchange on one GPU; absent peers are a sink, their records come from `peer_inject`."""
+        _lib.check(_lib.load().qpmpc_shard_peer_loopback(self._ensure()))
+        return self
+
+    def peer_inject(self, rank: int, record):
+        """Test hook: deliver peer `rank`'s shard record (and the stamp of the upcoming tick) before ticking."""
+        _lib.check(_lib.load().qpmpc_shard_peer_inject(self._ensure(), int(rank), _fp(_f32(record))))
+        return self
+
     def shard_partial(self, state, reference, contact_sequence, best, key, sigma=None, timing=None, nominal=None,
                       optimize_swing=None, noise=None, step_freqs=None) -> np.ndarray:
         """Rollouts + local reduction of this shard's slice; returns the shard record (floats) for a caller-side gather

@@ -1,0 +1,87 @@
+"""CEM elite selection on the device (histogram-assisted exact top-k, csrc/qpmpc_kernels.cuh block_topk_hist) and BASELINE
+config 3 at full size.  Elite indices must equal a stable ascending argsort of the costs (S:1075 | A:1115) exactly."""
+import numpy as np
+import pytest
+
+import quadruped_pympc_b200 as qp
+from quadruped_pympc_b200 import synthetic
+from helpers import LANES, make_pair, seeded_noise, seeded_freqs, run_both, assert_tick_parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('lanes', LANES)
+def test_config3_full_size(built, lanes):
+    """BASELINE config 3: HyQReal pace, CEM-MPPI with step-frequency adaptation, cubic, N = 50,000, 200 elites."""
+    oracle, ctrl, _ = make_pair('hyqreal1', 50000, control_parametrization='cubic_spline', sampling_method='cem_mppi',
+                                optimize_step_freq=True, lanes_per_sample=lanes)
+    sc = synthetic.scenario('hyqreal1', 'pace', seed=3)
+    best0 = np.zeros(oracle.P, np.float32)
+    sigma = np.full(oracle.P, 3.0, np.float32)
+    noise = seeded_noise(oracle, 3, sigma)
+    freqs = seeded_freqs(oracle, 3)
+    ref, got = run_both(oracle, ctrl, sc, best0, noise, sigma=sigma, freqs=freqs)
+    assert len(got['elite_indices']) == 200
+    assert_tick_parity(ref, got, cem=True, noise=noise)
+
+
+def _tick_cem(ctrl, sc, sigma, optimize_swing=1):
+    ctrl.with_newkey()
+    P = ctrl.num_control_parameters
+    out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], np.zeros(P, np.float32),
+                                      ctrl.master_key, sigma, sc['phase_signal'], sc['nominal_step_freq'], optimize_swing)
+    return np.asarray(out[6]), ctrl.last_elite_indices, ctrl.last_best_index
+
+
+@pytest.mark.parametrize('lanes', LANES)
+@pytest.mark.parametrize('N,adaptive,elite_k', [(1337, False, 0), (10000, False, 0), (10000, True, 0), (50000, True, 0),
+                                                (200000, False, 256), (300, True, 0), (7, False, 0)])
+def test_elites_are_the_stable_argsort_of_the_costs(built, N, adaptive, elite_k, lanes):
+    """Production mode (in-kernel Philox), several ticks per handle (the device histogram must come back clean)."""
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='cem_mppi', control_parametrization='linear_spline',
+                                     num_parallel_computations=N, optimize_step_freq=adaptive, elite_k=elite_k,
+                                     lanes_per_sample=lanes)
+    ctrl = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario('go2', 'trot', seed=5)
+    sigma = np.full(ctrl.num_control_parameters, 3.0, np.float32)
+    k = min(elite_k or (200 if adaptive else 10), N)
+    for _ in range(3):
+        costs, elite, best = _tick_cem(ctrl, sc, sigma)
+        want = np.argsort(costs, kind='stable')[:k]
+        np.testing.assert_array_equal(elite, want)
+        assert best == want[0]
+
+
+@pytest.mark.parametrize('lanes', LANES)
+@pytest.mark.parametrize('adaptive', [False, True])
+def test_heavy_ties_take_the_exact_slow_path(built, adaptive, lanes):
+    """All-zero Q: every fixed-gait cost is exactly 0 and the adaptive ones take three values (A:500), so the threshold
+    bin overflows the shared-memory candidate list and the selection must still be the stable argsort."""
+    N = 6000
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='cem_mppi', control_parametrization='zero_order',
+                                     num_parallel_computations=N, optimize_step_freq=adaptive, lanes_per_sample=lanes,
+                                     q_diag=(0.0,) * 12)
+    ctrl = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario('go2', 'trot', seed=9)
+    sigma = np.full(ctrl.num_control_parameters, 3.0, np.float32)
+    for _ in range(2):
+        costs, elite, best = _tick_cem(ctrl, sc, sigma)
+        assert len(np.unique(costs)) <= 3
+        want = np.argsort(costs, kind='stable')[:len(elite)]
+        np.testing.assert_array_equal(elite, want)
+        assert best == want[0]
+
+
+@pytest.mark.parametrize('lanes', LANES)
+def test_moderate_ties_are_resolved_by_index_digits(built, lanes):
+    """~N/3 equal costs with N/3 below the candidate capacity: refinement has to walk into the index digits."""
+    N = 3000
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='cem_mppi', control_parametrization='cubic_spline',
+                                     num_parallel_computations=N, optimize_step_freq=True, lanes_per_sample=lanes,
+                                     q_diag=(0.0,) * 12)
+    ctrl = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario('go2', 'pace', seed=1)
+    sigma = np.full(ctrl.num_control_parameters, 3.0, np.float32)
+    costs, elite, best = _tick_cem(ctrl, sc, sigma)
+    assert len(elite) == 200
+    np.testing.assert_array_equal(elite, np.argsort(costs, kind='stable')[:200])

@@ -64,3 +64,81 @@ def test_sharded_philox_equals_unsharded(built):
     np.testing.assert_allclose(out[4], whole[4], rtol=1e-6)
     np.testing.assert_allclose(out[3], whole[3], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(out[0], whole[0], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('method,adaptive,world', [('random_sampling', False, 2), ('mppi', False, 3), ('cem_mppi', False, 8),
+                                                   ('mppi', True, 2), ('cem_mppi', True, 4)])
+def test_fused_peer_exchange_loopback(built, method, adaptive, world, lanes):
+    """The collective fused into the tick kernel (qpmpc_tick.cuh peer_exchange), on ONE GPU: each shard in turn runs
+    its fused tick with the peers' records delivered to its mailbox beforehand (no kernel waits on a running kernel).
+    Every shard must return the oracle's result, bit-identical across shards; repeated for three ticks so that both
+    mailbox parities and the stamp sequence are exercised."""
+    N = 2501
+    oracle, _, _ = make_pair('go2', N, control_parametrization='cubic_spline', sampling_method=method,
+                             optimize_step_freq=adaptive)
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=N, control_parametrization='cubic_spline',
+                                     sampling_method=method, optimize_step_freq=adaptive, lanes_per_sample=lanes)
+    shards = [qp.Sampling_MPC(cfg, shard_rank=r, shard_world=world).peer_loopback() for r in range(world)]
+    sc = synthetic.scenario('go2', 'trot', seed=9)
+    rng = np.random.RandomState(3)
+    best0 = (0.5 * rng.randn(oracle.P)).astype(np.float32)
+    sigma = np.linspace(1.0, 4.0, oracle.P).astype(np.float32) if method == 'cem_mppi' else None
+    for tick in range(3):
+        noise = seeded_noise(oracle, 5 + tick, sigma)
+        freqs = seeded_freqs(oracle, 5 + tick) if adaptive else None
+        ref = oracle.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, noise, sigma=sigma,
+                                     timing=sc['phase_signal'], nominal_step_frequency=sc['nominal_step_freq'],
+                                     optimize_swing=1, step_frequencies=freqs)
+        key = np.array([42, 1 + tick], np.uint32)
+        recs = [s.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sigma=sigma,
+                                timing=sc['phase_signal'], nominal=sc['nominal_step_freq'], optimize_swing=1,
+                                noise=noise, step_freqs=freqs) for s in shards]
+        outs = []
+        for me, s in enumerate(shards):
+            for w in range(world):
+                if w != me:
+                    s.peer_inject(w, recs[w])
+            args = (sigma, sc['phase_signal'], sc['nominal_step_freq'], 1) if method == 'cem_mppi' else \
+                   (sc['phase_signal'], sc['nominal_step_freq'], 1)
+            outs.append(s.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *args,
+                                                 noise=noise, step_freqs=freqs))
+        costs = np.concatenate([np.asarray(o[6]) for o in outs])
+        for s, o in zip(shards, outs):
+            got = dict(nmpc_GRFs=o[0], nmpc_predicted_state=o[2], best_control_parameters=o[3], best_cost=o[4],
+                       best_freq=o[5], costs=costs, best_index=s.last_best_index)
+            if method == 'cem_mppi':
+                got['new_sigma_cem_mppi'], got['elite_indices'] = o[7], s.last_elite_indices
+            assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
+        for o in outs[1:]:
+            assert np.array_equal(o[3], outs[0][3]) and np.array_equal(o[0], outs[0][0])
+
+
+def test_fused_peer_exchange_production_mode_loopback(built):
+    """Direct I/O + in-kernel Philox through the fused exchange equals the unsharded tick."""
+    N, world = 10000, 2
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=N, sampling_method='mppi')
+    sc = synthetic.scenario('go2', 'trot', seed=2)
+    key = np.array([42, 7], np.uint32)
+    best0 = np.zeros(96, np.float32)
+    whole_ctrl = qp.Sampling_MPC(cfg)
+    whole = whole_ctrl.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sc['phase_signal'], 1.4, 0)
+    shards = [qp.Sampling_MPC(cfg, shard_rank=r, shard_world=world).peer_loopback() for r in range(world)]
+    recs = [s.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key) for s in shards]
+    for me, s in enumerate(shards):
+        s.peer_inject(1 - me, recs[1 - me])
+        out = s.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sc['phase_signal'], 1.4, 0)
+        assert s.last_best_index == whole_ctrl.last_best_index
+        np.testing.assert_allclose(out[4], whole[4], rtol=1e-6)
+        np.testing.assert_allclose(out[3], whole[3], rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(out[0], whole[0], rtol=1e-4, atol=1e-4)
+
+
+def test_peer_attach_refuses_two_shards_on_one_gpu(built):
+    """Two waiting kernels on one GPU are not guaranteed to run at the same time: attach must refuse."""
+    from quadruped_pympc_b200 import _lib
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=1000, sampling_method='mppi')
+    a, b = (qp.Sampling_MPC(cfg, shard_rank=r, shard_world=2) for r in range(2))
+    blobs = [a.peer_export(), b.peer_export()]
+    with pytest.raises(_lib.QpmpcError, match='same GPU'):
+        a.peer_attach(blobs)

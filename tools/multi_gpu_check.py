@@ -40,6 +40,7 @@ def main():
     ap.add_argument('--ticks', type=int, default=300)
     ap.add_argument('--out', default='')
     ap.add_argument('--sizes', default='1000,10000,100000,1000000')
+    ap.add_argument('--exchange', default='peer,nccl')
     args = ap.parse_args()
     rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
     torch.cuda.set_device(local)
@@ -50,7 +51,8 @@ def main():
     cases += [('go2', 'trot', 'random_sampling', 'zero_order', False, 10000),
               ('hyqreal1', 'pace', 'cem_mppi', 'cubic_spline', True, 50000),
               ('go2', 'trot', 'cem_mppi', 'linear_spline', False, 10000)]
-    for exchange in ('peer', 'nccl'):
+    t_start = time.perf_counter()
+    for exchange in args.exchange.split(','):
         for robot, gait, method, param, adaptive, N in cases:
             cfg = qp.SamplerConfig.for_robot(robot, sampling_method=method, control_parametrization=param,
                                              num_parallel_computations=N, optimize_step_freq=adaptive, device=local)
@@ -101,7 +103,8 @@ def main():
                         'param': param, 'adaptive': adaptive, 'N': N, 'parity_ok': bool(ok), 'ranks_bit_identical': bool(identical),
                         'detail': detail, 'ticks': args.ticks, 'p50_us': float(np.percentile(lat, 50) * 1e6),
                         'p99_us': float(np.percentile(lat, 99) * 1e6),
-                        'rollout_steps_per_s': args.ticks * N * ctrl.horizon / float(tot.item())}
+                        'rollout_steps_per_s': args.ticks * N * ctrl.horizon / float(tot.item()),
+                        'elapsed_s': round(time.perf_counter() - t_start, 1)}
                 print(json.dumps(line), flush=True)
                 lines.append(line)
             del ctrl
