@@ -25,6 +25,8 @@
 
 #define ORC_MAX_H 64
 #define ORC_MAX_NS 16
+#define ORC_PHILOX_K0 0xA4093822u   /* fixed key of the product's generator (csrc/qpmpc_kernels.cuh PHILOX_K0/K1) */
+#define ORC_PHILOX_K1 0x299F31D0u
 
 enum { ORC_ZERO_ORDER = 0, ORC_LINEAR = 1, ORC_CUBIC = 2 };
 enum { ORC_RANDOM_SAMPLING = 0, ORC_MPPI = 1, ORC_CEM_MPPI = 2 };
@@ -345,7 +347,8 @@ void orc_compute_control(const orc_cfg *c, const float *state, const float *ref,
 
 /* ===================================================================================================
  * Host mirror of the product's noise generator (NOT reference code; see file header).
- * Philox4x32-10 (Salmon et al., SC'11), counter = (quad, row, tick, stream), key = (seed, robot).
+ * Philox4x32-10 (Salmon et al., SC'11), counter = (quad | stream << 8 | robot << 9, row, tick, seed), fixed key
+ * (ORC_PHILOX_K0, ORC_PHILOX_K1) -- the same convention as csrc/qpmpc_kernels.cuh.
  * =================================================================================================== */
 static inline void philox_round(uint32_t c[4], const uint32_t k[2]) {
     uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
@@ -405,7 +408,7 @@ void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_
             else if (i >= 1 + k) { seg = 1; j = i - 1 - k; }
         }
         for (int qd = 0; qd < P / 4; ++qd) {
-            uint32_t ctr[4] = {(uint32_t)qd, (uint32_t)j, tick, 0u}, key[2] = {seed, robot}, r[4];
+            uint32_t ctr[4] = {(uint32_t)qd | (robot << 9), (uint32_t)j, tick, seed}, key[2] = {ORC_PHILOX_K0, ORC_PHILOX_K1}, r[4];
             orc_philox4x32_10(ctr, key, r);
             float z[4];
             box_muller(r[0], r[1], &z[0], &z[1]);
@@ -430,7 +433,7 @@ void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_
 /* per-sample choice index in {0,1,2} (stream 1): floor(bits * 3 / 2^32) */
 void orc_freq_choice(uint32_t seed, uint32_t robot, uint32_t tick, int row_begin, int row_end, int32_t *choice) {
     for (int i = row_begin; i < row_end; ++i) {
-        uint32_t ctr[4] = {0u, (uint32_t)i, tick, 1u}, key[2] = {seed, robot}, r[4];
+        uint32_t ctr[4] = {0x100u | (robot << 9), (uint32_t)i, tick, seed}, key[2] = {ORC_PHILOX_K0, ORC_PHILOX_K1}, r[4];
         orc_philox4x32_10(ctr, key, r);
         choice[i - row_begin] = (int32_t)(((uint64_t)r[0] * 3u) >> 32);
     }

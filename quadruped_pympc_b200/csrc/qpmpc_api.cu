@@ -58,7 +58,7 @@ __global__ void noise_export_kernel(const __grid_constant__ KParams kp, uint32_t
 template <int METHOD>
 __global__ void freq_export_kernel(const __grid_constant__ KParams kp, const float *in_rec, float *dst) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kp.N; i += gridDim.x * blockDim.x)
-        dst[i] = sample_step_freq<METHOD>(kp, in_rec, 0, i);
+        dst[i] = sample_step_freq<METHOD>(kp, in_rec, kp.seed, kp.robot_base, 0, i);
 }
 
 __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
@@ -386,6 +386,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     kp.in = h->kin; kp.out = h->kout; kp.costs = h->d_costs; kp.blk_recs = h->d_blk;
     kp.shard_send = h->d_send; kp.shard_recv = h->d_recv; kp.counters = h->d_counters; kp.cem_hist = h->d_cem_hist;
     kp.noise = nullptr; kp.freqs = nullptr;
+    kp.seed = cfg->seed; kp.robot_base = (uint32_t)cfg->robot_base;
     h->direct = (cfg->io_mode == QPMPC_IO_DIRECT && h->R == 1 && kp.in_stride <= PACKET_MAX);   // W > 1: peer-exchange ticks only
     if (h->direct) {
         CKH(cudaHostAlloc((void **)&h->h_dout, (kp.out_stride + 4) * sizeof(float), cudaHostAllocMapped));
@@ -417,6 +418,8 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     if (h->cfg.adaptive && !in->phase_signal) return fail(QPMPC_ERR_INVALID, "phase_signal is required by the gait-adaptive controller");
     rec[IN_NOMFREQ] = in->nominal_step_freq;
     rec[IN_OPTSWING] = u2f((uint32_t)in->optimize_swing);
+    if (r == 0) h->kp.seed = in->key[0];             // Philox key word 0 travels in kernel-parameter space (block-uniform)
+    else if (in->key[0] != h->kp.seed) return fail(QPMPC_ERR_INVALID, "all robots of one batch must share key[0] (robot %d differs); streams differ by robot id", r);
     rec[IN_SEED] = u2f(in->key[0]);
     rec[IN_TICK] = u2f(in->key[1]);
     rec[IN_ROBOT] = u2f((uint32_t)(h->cfg.robot_base + r));   // global robot id = Philox key word 1
@@ -688,6 +691,7 @@ extern "C" int qpmpc_generate_step_freqs(qpmpc_handle *h, int robot, const uint3
     CK(cudaMemcpyAsync(h->d_in, rec, (size_t)h->kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     KParams kp = h->kp;
     kp.freq_injected = 0;
+    kp.seed = key[0]; kp.robot_base = (uint32_t)robot;
     const int threads = 256, blocks = std::min((h->N + threads - 1) / threads, 148 * 8);
     switch (h->cfg.method) {
         case QPMPC_RANDOM_SAMPLING: freq_export_kernel<RANDOM_SAMPLING><<<blocks, threads, 0, h->stream>>>(kp, h->d_in, h->d_freqs); break;

@@ -83,6 +83,8 @@ struct KParams {
     float *host_out;                        // mapped pinned host alias: [out_stride floats][stamp], or NULL
     float packet[PACKET_MAX];
     // ---- peer exchange of a sample-sharded controller (fused collective, qpmpc_tick.cuh peer_exchange) ----
+    uint32_t seed;                          // Philox counter word 3 of this launch (all robots of a batch share it)
+    uint32_t robot_base;                    // global robot id = robot_base + blockIdx.y (< 2^23), part of counter word 0
     int peer_world;                         // > 1: the last block pushes its shard record into every peer's mailbox over
     int peer_rank;                          //      NVLink, waits for the peers' records and finishes in the same launch
     float *peer_mbox[MAX_PEERS];            // mailbox base of every rank (own entry = local memory): see peer_exchange
@@ -102,8 +104,14 @@ __device__ __forceinline__ void phase_mark(const KParams &kp, int slot) {
 }
 
 // ======================================================================================================
-// RNG: Philox4x32-10, counter = (quad, row, tick, stream), key = (seed, robot)   (host mirror: oracle/sampling_oracle.c)
+// RNG: Philox4x32-10 in counter mode under a FIXED key (host mirror: oracle/sampling_oracle.c):
+//   counter = (quad | stream << 8 | robot << 9,  row,  tick,  seed),   key = (PHILOX_K0, PHILOX_K1)
+// Everything that varies -- per thread, per robot, per tick, per seed -- sits in the 128-bit counter, which enters once,
+// in round 0; the key is a compile-time constant, so the 2 x 10 round keys are immediates and cost no instruction
+// (keyed by (seed, robot) they cost 2 integer adds per round per thread: 6 % of the whole tick, ncu r1d).  A fixed-key
+// Philox is a fixed bijection of the counter space: distinct (quad, stream, robot, row, tick, seed) -> distinct blocks.
 // ======================================================================================================
+constexpr uint32_t PHILOX_K0 = 0xA4093822u, PHILOX_K1 = 0x299F31D0u;   // digits of pi (nothing up the sleeve)
 __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
@@ -145,50 +153,60 @@ __device__ __forceinline__ float4 normal_quad(uint4 r) {
 // One quad (4 consecutive knots) of additional_random_parameters for global row i.
 //  random_sampling S:647-677: rows [1,1+k) s0*N, [1+k,1+2k) s1*N (same key => same normals), [1+2k,N) U(-s2,s2)
 //  mppi S:806-812: s*N on rows 1..N-1 ; cem_mppi S:951-958: N*sigma[p] ; row 0 is always zero.
+// NoiseRow: what depends on the row only (computed once per sample, outside the loop over quads).
+struct NoiseRow { uint32_t j; int seg; float scale; bool zero; };
+
 template <int METHOD>
-__device__ __forceinline__ float4 noise_quad(const KParams &kp, uint32_t seed, uint32_t robot, uint32_t tick, int i,
-                                             int q, const float *s_sigma) {
-    if (i == 0) return make_float4(0.f, 0.f, 0.f, 0.f);
-    int seg = 0, j = i - 1;
+__device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
+    NoiseRow nr;
+    nr.zero = (i == 0); nr.seg = 0; nr.j = (uint32_t)(i - 1); nr.scale = kp.sigma_mppi;
     if (METHOD == RANDOM_SAMPLING) {
         const int k = kp.N / 3;
-        if (i >= 1 + 2 * k) { seg = 2; j = i - 1 - 2 * k; }
-        else if (i >= 1 + k) { seg = 1; j = i - 1 - k; }
+        if (i >= 1 + 2 * k) { nr.seg = 2; nr.j = (uint32_t)(i - 1 - 2 * k); }
+        else if (i >= 1 + k) { nr.seg = 1; nr.j = (uint32_t)(i - 1 - k); }
+        nr.scale = kp.sigma_rs[nr.seg];
     }
-    uint4 r = philox4x32_10((uint32_t)q, (uint32_t)j, tick, 0u, seed, robot);
+    return nr;
+}
+
+template <int METHOD>
+__device__ __forceinline__ float4 noise_quad(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
+                                             const float *s_sigma) {
+    if (nr.zero) return make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 r = philox4x32_10((uint32_t)q | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
     float4 v;
-    if (METHOD == RANDOM_SAMPLING) {
-        if (seg == 2) {
-            const float s2 = kp.sigma_rs[2];
-            const float span = s2 - (-s2);
-            v.x = fmaxf(fmaf(u01_from_bits(r.x), span, -s2), -s2);
-            v.y = fmaxf(fmaf(u01_from_bits(r.y), span, -s2), -s2);
-            v.z = fmaxf(fmaf(u01_from_bits(r.z), span, -s2), -s2);
-            v.w = fmaxf(fmaf(u01_from_bits(r.w), span, -s2), -s2);
-        } else {
-            const float s = kp.sigma_rs[seg];
-            const float4 z = normal_quad(r);
-            v.x = s * z.x; v.y = s * z.y; v.z = s * z.z; v.w = s * z.w;
-        }
-    } else if (METHOD == MPPI) {
-        const float s = kp.sigma_mppi;
-        const float4 z = normal_quad(r);
-        v.x = s * z.x; v.y = s * z.y; v.z = s * z.z; v.w = s * z.w;
-    } else {
+    if (METHOD == RANDOM_SAMPLING && nr.seg == 2) {
+        const float s2 = nr.scale;
+        const float span = s2 - (-s2);
+        v.x = fmaxf(fmaf(u01_from_bits(r.x), span, -s2), -s2);
+        v.y = fmaxf(fmaf(u01_from_bits(r.y), span, -s2), -s2);
+        v.z = fmaxf(fmaf(u01_from_bits(r.z), span, -s2), -s2);
+        v.w = fmaxf(fmaf(u01_from_bits(r.w), span, -s2), -s2);
+    } else if (METHOD == CEM_MPPI) {
         const float4 z = normal_quad(r);
         v.x = z.x * s_sigma[4 * q + 0]; v.y = z.y * s_sigma[4 * q + 1];
         v.z = z.z * s_sigma[4 * q + 2]; v.w = z.w * s_sigma[4 * q + 3];
+    } else {
+        const float s = nr.scale;
+        const float4 z = normal_quad(r);
+        v.x = s * z.x; v.y = s * z.y; v.z = s * z.z; v.w = s * z.w;
     }
     return v;
+}
+// convenience form for one-off rows (finish stage, export kernels)
+template <int METHOD>
+__device__ __forceinline__ float4 noise_quad(const KParams &kp, uint32_t seed, uint32_t robot, uint32_t tick, int i,
+                                             int q, const float *s_sigma) {
+    return noise_quad<METHOD>(noise_row<METHOD>(kp, i), seed, robot, tick, q, s_sigma);
 }
 
 // Per-sample step frequency (row a15).  A:688-692 (random_sampling) | A:835-838 (mppi) | A:994-1000 (cem_mppi)
 template <int METHOD>
-__device__ __forceinline__ float sample_step_freq(const KParams &kp, const float *s_in, int robot_slot, int i) {
+__device__ __forceinline__ float sample_step_freq(const KParams &kp, const float *s_in, uint32_t seed, uint32_t robot,
+                                                  int robot_slot, int i) {
     if (kp.freq_injected) return __ldg(kp.freqs + (size_t)robot_slot * kp.N + i);
-    const uint32_t seed = __float_as_uint(s_in[IN_SEED]), tick = __float_as_uint(s_in[IN_TICK]);
-    const uint32_t robot = __float_as_uint(s_in[IN_ROBOT]);
-    uint4 r = philox4x32_10(0u, (uint32_t)i, tick, 1u, seed, robot);
+    const uint32_t tick = __float_as_uint(s_in[IN_TICK]);
+    uint4 r = philox4x32_10(0x100u | (robot << 9), (uint32_t)i, tick, seed, PHILOX_K0, PHILOX_K1);
     const int c = (int)__umulhi(r.x, 3u);
     const float nominal = s_in[IN_NOMFREQ];
     const int opt = __float_as_int(s_in[IN_OPTSWING]);
@@ -221,26 +239,44 @@ __device__ __forceinline__ void sincos_small(float x, float *sn, float *cs) {
     }
 }
 
-// S:270-314 (box friction pyramid, same comparison order; NaN fz -> fz_min)
+// S:270-314 (box friction pyramid, same comparison order).  where(x > lo, x, lo) == fmaxf(x, lo) and where(x < hi, x, hi)
+// == fminf(x, hi) for every input the reference can produce, NaN included (a NaN force takes the bound, as `where`
+// does; only the sign of a zero can differ, which no later product can see): one FMNMX instead of FSETP + FSEL.
 __device__ __forceinline__ void clamp_leg(const KParams &kp, float &fx, float &fy, float &fz) {
-    fz = fz > kp.fz_min ? fz : kp.fz_min;
-    fz = fz < kp.fz_max ? fz : kp.fz_max;
-    const float lo = -kp.mu * fz, hi = kp.mu * fz;
-    fx = fx > lo ? fx : lo; fx = fx < hi ? fx : hi;
-    fy = fy > lo ? fy : lo; fy = fy < hi ? fy : hi;
+    fz = fminf(fmaxf(fz, kp.fz_min), kp.fz_max);
+    const float hi = kp.mu * fz, lo = -hi;
+    fx = fminf(fmaxf(fx, lo), hi);
+    fy = fminf(fmaxf(fy, lo), hi);
 }
 
 // Fx..: sum of stance forces; tx..: sum of (foot - com) x F (world frame), M:111-118,132-135
+// Yaw is unweighted and unbounded, but every sample of a tick starts from the same yaw0: sin/cos(yaw0) are computed once
+// per block (s_yaw = {yaw0, sin yaw0, cos yaw0}, stage_inputs) and each step only needs the small-angle polynomials of
+// the drift d = yaw - yaw0 plus the angle-addition identities (~16 instructions instead of sincosf's ~35, <= 2 ulp).
+__device__ __forceinline__ void sincos_yaw(float yaw, const float *s_yaw, float *sn, float *cs) {
+    const float d = yaw - s_yaw[0];
+    if (fabsf(d) <= 0.78539816f) {
+        float sd, cd;
+        sincos_small(d, &sd, &cd);
+        const float s0 = s_yaw[1], c0 = s_yaw[2];
+        *sn = fmaf(s0, cd, c0 * sd);
+        *cs = fmaf(c0, cd, -(s0 * sd));
+    } else {
+        sincosf(yaw, sn, cs);
+    }
+}
+
 __device__ __forceinline__ float srbd_step(const KParams &kp, Body &b, float Fx, float Fy, float Fz, float tx, float ty,
-                                           float tz, float dt, const float *ref) {
+                                           float tz, float dt, const float *ref, const float *s_yaw) {
     const float ax = kp.inv_m * Fx, ay = kp.inv_m * Fy, az = fmaf(kp.inv_m, Fz, -9.81f);       // M:118
     float sr, cr, sp, cp, sy, cy;
     sincos_small(b.roll, &sr, &cr);
     sincos_small(b.pitch, &sp, &cp);
-    sincosf(b.yaw, &sy, &cy);
+    sincos_yaw(b.yaw, s_yaw, &sy, &cy);
     // inverse of the conjugate Euler-rate matrix by cofactors with its structural zeros dropped, M:124-130,137
     const float det = (cp * cr) * cr + sr * (cp * sr);
-    const float rd = 1.0f / det;
+    float rd;                                             // 1 / det on the SFU (<= 1 ulp; det = cos(pitch) is O(1))
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rd) : "f"(det));
     const float e01 = (sr * sp) * rd, e02 = (cr * sp) * rd, e11 = (cp * cr) * rd, e12 = -(cp * sr) * rd;
     const float e21 = sr * rd, e22 = cr * rd;
     const float droll = b.wx + e01 * b.wy + e02 * b.wz;
@@ -310,6 +346,7 @@ __device__ __forceinline__ void add_leg(const KParams &kp, const Body &b, const 
 // S:388-402 and M:111-116).  s_fref[n] = mass*9.81 / n_stance(n) (S:377-380).
 template <int PARAM>
 __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s_in, const float *s_fref, const float *tcol) {
+    const float *s_yaw = s_fref + MAX_H;
     const float *s_best = s_in + kp.off_best;
     const float *s_contact = s_in + IN_CONTACT;
     const float *ref = s_in + IN_REF;
@@ -372,7 +409,7 @@ __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s
                 add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }
         }
-        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);   // S:446-451,491
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw);   // S:446-451,491
     }
     return cost;
 }
@@ -419,7 +456,7 @@ __device__ __forceinline__ void spline_dyn(const KParams &kp, const float *s_bes
 // Gait-adaptive rollout (A:326-501): per-sample contact sequence from the phase clock (G:68-89,136-151),
 // per-leg stance counters as spline clocks, plus the step-frequency cost A:500.
 template <int PARAM>
-__device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float *s_in, const float *tcol, float freq) {
+__device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float *s_in, const float *s_yaw, const float *tcol, float freq) {
     const float *s_best = s_in + kp.off_best;
     const float *ref = s_in + IN_REF;
     const float *feet = s_in + IN_STATE + 12;
@@ -471,7 +508,7 @@ __device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float
                 add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }
         }
-        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw);
     }
     const float df = freq - 1.3f;
     cost += df * 100.0f * df;                                  // A:500
@@ -524,7 +561,7 @@ __device__ __forceinline__ float block_sum(float v, float *s_red) {
 // spline(best_leg, 0.0, 1): zero-order -> p[0],p[H],p[2H]; linear -> p[0],p[ns+1],p[2(ns+1)]; cubic (q=0) -> p[1],p[5],p[9].
 // Executed by one thread.  best: P floats (shared or global).
 template <int PARAM>
-__device__ void tail_grf_pred(const KParams &kp, const float *s_in, const float *best, float *out) {
+__device__ void tail_grf_pred(const KParams &kp, const float *s_in, const float *s_yaw, const float *best, float *out) {
     const float *s_contact = s_in + IN_CONTACT;
     const int H = kp.H;
     float c[4], nst;
@@ -551,7 +588,7 @@ __device__ void tail_grf_pred(const KParams &kp, const float *s_in, const float 
         }
     }
     const float zero_ref[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    (void)srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[0], zero_ref);   // S:784
+    (void)srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[0], zero_ref, s_yaw);   // S:784
     out[OUT_PRED + 0] = b.px; out[OUT_PRED + 1] = b.py; out[OUT_PRED + 2] = b.pz;
     out[OUT_PRED + 3] = b.vx; out[OUT_PRED + 4] = b.vy; out[OUT_PRED + 5] = b.vz;
     out[OUT_PRED + 6] = b.roll; out[OUT_PRED + 7] = b.pitch; out[OUT_PRED + 8] = b.yaw;

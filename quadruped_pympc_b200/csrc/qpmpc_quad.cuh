@@ -46,6 +46,7 @@ __device__ __forceinline__ void leg_wrench(const KParams &kp, const Body &b, con
 template <int PARAM>
 __device__ __forceinline__ float rollout_fixed_quad(const KParams &kp, const float *s_in, const float *s_fref, const float *tleg,
                                                     int leg) {
+    const float *s_yaw = s_fref + MAX_H;
     const float *s_bleg = s_in + kp.off_best + leg * kp.P_leg;
     const float *s_contact = s_in + IN_CONTACT + leg * kp.H;
     const float *ref = s_in + IN_REF;
@@ -97,7 +98,7 @@ __device__ __forceinline__ float rollout_fixed_quad(const KParams &kp, const flo
         }
         Fx = quad_sum(Fx); Fy = quad_sum(Fy); Fz = quad_sum(Fz);
         tx = quad_sum(tx); ty = quad_sum(ty); tz = quad_sum(tz);
-        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);   // S:446-451,491
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw);   // S:446-451,491
     }
     return cost;
 }
@@ -143,8 +144,8 @@ __device__ __forceinline__ void spline_dyn_quad(const KParams &kp, const float *
 
 // Gait-adaptive rollout (A:326-501), lane `leg`: own phase clock (G:68-89), stance counter and spline clock.
 template <int PARAM>
-__device__ __forceinline__ float rollout_adaptive_quad(const KParams &kp, const float *s_in, const float *tleg, int leg,
-                                                       float freq) {
+__device__ __forceinline__ float rollout_adaptive_quad(const KParams &kp, const float *s_in, const float *s_yaw,
+                                                       const float *tleg, int leg, float freq) {
     const float *s_bleg = s_in + kp.off_best + leg * kp.P_leg;
     const float *ref = s_in + IN_REF;
     const float *foot = s_in + IN_STATE + 12 + 3 * leg;
@@ -178,7 +179,7 @@ __device__ __forceinline__ float rollout_adaptive_quad(const KParams &kp, const 
         }
         Fx = quad_sum(Fx); Fy = quad_sum(Fy); Fz = quad_sum(Fz);
         tx = quad_sum(tx); ty = quad_sum(ty); tz = quad_sum(tz);
-        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref);
+        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw);
     }
     const float df = freq - 1.3f;
     cost += df * 100.0f * df;                                 // A:500
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     if (blk == 0) phase_mark(kp, 0);
     stage_inputs<QTB>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
-    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
+    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + slot;
     const float *tleg = tcol + leg * kp.P_leg * QTS;
@@ -225,8 +226,9 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             __syncthreads();
         } else {
             if (active) {
+                const NoiseRow nr = noise_row<METHOD>(kp, gi);
                 for (int q = q_lo; q < q_hi; ++q) {
-                    const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, gi, q, s_sigma);
+                    const float4 e = noise_quad<METHOD>(nr, seed, robot, tick, q, s_sigma);
                     tcol[(4 * q) * QTS] = e.x; tcol[(4 * q + 1) * QTS] = e.y; tcol[(4 * q + 2) * QTS] = e.z; tcol[(4 * q + 3) * QTS] = e.w;
                 }
             } else {
@@ -241,8 +243,8 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
         float cost = CUDART_INF_F;
         if (ADAPTIVE) {
             // inactive quads run along (shuffles need the whole warp) on zero noise; their cost is discarded
-            const float freq = active ? sample_step_freq<METHOD>(kp, s.in, r, gi) : 1.3f;
-            cost = rollout_adaptive_quad<PARAM>(kp, s.in, tleg, leg, freq);
+            const float freq = active ? sample_step_freq<METHOD>(kp, s.in, seed, robot, r, gi) : 1.3f;
+            cost = rollout_adaptive_quad<PARAM>(kp, s.in, s.yaw, tleg, leg, freq);
         } else {
             cost = rollout_fixed_quad<PARAM>(kp, s.in, s.fref, tleg, leg);
         }
@@ -267,15 +269,18 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             const float m_new = fminf(m_run, cmin);
             const float scale_old = (m_run == CUDART_INF_F) ? 0.0f : expf(-(m_run - m_new));
             const float w = active ? expf(-(cost - m_new)) : 0.0f;   // exp(-(c - beta)/T), T = 1, S:828-830
-            __syncthreads();
-            if (leg == 0) s.w[slot] = w;
-            const float s_tile = block_sum<QTB>(leg == 0 ? w : 0.0f, s.red);   // barriers inside publish s.w and the tile
+            float s_tile;
+            const int nnz = compact_weights<QTB>(w, slot, leg == 0, s, s_tile);   // its barriers also publish the tile
             s_run = fmaf(s_run, scale_old, s_tile);
+            const float2 *wi = reinterpret_cast<const float2 *>(s.w);
             for (int p = t; p < kp.P; p += QTB) {
                 const float *rowp = s.tile + p * QTS;
                 float acc = 0.0f;
-#pragma unroll 8
-                for (int e = 0; e < QS; ++e) acc = fmaf(s.w[e], rowp[e], acc);
+#pragma unroll 4
+                for (int j = 0; j < nnz; ++j) {
+                    const float2 we = wi[j];
+                    acc = fmaf(we.x, rowp[__float_as_int(we.y)], acc);
+                }
                 s.v[p] = fmaf(s.v[p], scale_old, acc);
             }
         }

@@ -11,13 +11,14 @@ constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogra
 
 // shared-memory carve-up (float offsets); every region starts 16-byte aligned
 struct Smem {
-    float *in, *fref, *w, *v, *red, *tile;
+    float *in, *fref, *yaw, *w, *v, *red, *tile;
     int *idx;                               // MAX_ELITE elite indices (CEM refit)
     __device__ Smem(float *base, const KParams &kp, int nt = TB) {
         in = base;
         fref = in + kp.in_stride;
-        w = fref + MAX_H;
-        v = w + nt;
+        yaw = fref + MAX_H;                 // {yaw0, sin yaw0, cos yaw0, -}: directly behind fref (rollouts rely on it)
+        w = yaw + 4;                        // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
+        v = w + 2 * nt;
         red = v + kp.P;
         idx = reinterpret_cast<int *>(red + 16);
         tile = red + 16 + MAX_ELITE;
@@ -27,7 +28,7 @@ struct Smem {
 // the CEM elite refit, nt / 4 + 1 for the four-lanes-per-sample kernel without CEM)
 __host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB, int tile_cols = TS) {
     const size_t tile = (size_t)P * tile_cols > (size_t)SCRATCH_FLOATS ? (size_t)P * tile_cols : (size_t)SCRATCH_FLOATS;
-    return (size_t)in_stride + MAX_H + nt + P + 16 + MAX_ELITE + tile + 4;
+    return (size_t)in_stride + MAX_H + 4 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
 }
 
 template <int NT>
@@ -41,6 +42,12 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
         const int n = threadIdx.x, H = kp.H;
         const float nst = ((c[n] + c[H + n]) + c[2 * H + n]) + c[3 * H + n];
         s.fref[n] = kp.mg / nst;
+    }
+    if (threadIdx.x == TB - 1) {    // block-uniform yaw0 and its sine / cosine (sincos_yaw)
+        const float y0 = s.in[IN_STATE + 8];
+        float sn, cs;
+        sincosf(y0, &sn, &cs);
+        s.yaw[0] = y0; s.yaw[1] = sn; s.yaw[2] = cs; s.yaw[3] = 0.0f;
     }
     __syncthreads();
 }
@@ -210,7 +217,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     // premerged: the caller (fused single-shard tick) has just produced (M, IDX, S, s.v) in shard_reduce
     if (!premerged) merge_records<METHOD, NT>(recs, world, rec_stride, kp.P, s, M, IDX, S);
     float *out = kp.out + (size_t)r * kp.out_stride;
-    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
+    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_best = s.in + kp.off_best;
     const float *s_sigma = s.in + kp.off_sigma;
     // ---- new best into s.v ----
@@ -236,11 +243,11 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + kp.off_best + p] = s.v[p];
     }
     if (t == 0) {
-        tail_grf_pred<PARAM>(kp, s.in, s.v, out);
+        tail_grf_pred<PARAM>(kp, s.in, s.yaw, s.v, out);
         out[OUT_BESTCOST] = M;
         out[OUT_BESTIDX] = __int_as_float(IDX);
         float bf;
-        if (ADAPTIVE) bf = sample_step_freq<METHOD>(kp, s.in, r, IDX);             // A:705,861,1022
+        if (ADAPTIVE) bf = sample_step_freq<METHOD>(kp, s.in, seed, robot, r, IDX);   // A:705,861,1022
         else bf = (METHOD == CEM_MPPI) ? 1.65f : 1.4f;                               // S:786,930,1083
         out[OUT_BESTFREQ] = bf;
         if (METHOD != CEM_MPPI) out[OUT_NELITE] = __int_as_float(0);
@@ -349,6 +356,26 @@ __device__ __forceinline__ void publish_to_host(const KParams &kp, int r) {
     }
 }
 
+// Publish the tile's softmax weights for the weighted knot sum: only the non-zero ones (at T = 1 most weights underflow to
+// exactly 0), as (weight, sample slot) pairs in ascending slot order -- the same addends in the same
+// order as a loop over all slots that skips zeros, so the sum is bit-identical.  Returns the pair count; s_tile = sum of
+// the tile's weights (fixed order).  `owner`: this thread holds the weight of sample `slot` (one lane per sample).
+template <int NT>
+__device__ __forceinline__ int compact_weights(float w, int slot, bool owner, const Smem &s, float &s_tile) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const bool nzb = owner && (w != 0.0f);
+    const unsigned int nz = __ballot_sync(0xffffffffu, nzb);
+    __shared__ int s_wcnt[NT / 32];
+    if (lane == 0) s_wcnt[wid] = __popc(nz);
+    s_tile = block_sum<NT>(owner ? w : 0.0f, s.red);                   // its two barriers publish s_wcnt
+    int off = __popc(nz & ((1u << lane) - 1u)), total = 0;
+#pragma unroll
+    for (int k = 0; k < NT / 32; ++k) { const int c = s_wcnt[k]; total += c; if (k < wid) off += c; }
+    if (nzb) reinterpret_cast<float2 *>(s.w)[off] = make_float2(w, __int_as_float(slot));
+    __syncthreads();
+    return total;
+}
+
 // ------------------------------------------------------------------------------------------------------
 // Fused collective of a sample-sharded controller (one exchange step per tick): instead of a separate
 // all-gather launch, the last block of each shard stores its record straight into every peer GPU's mailbox (plain
@@ -447,7 +474,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
     if (blk == 0) phase_mark(kp, 0);
     stage_inputs<TB>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
-    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), tick = __float_as_uint(s.in[IN_TICK]), robot = __float_as_uint(s.in[IN_ROBOT]);
+    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + t;
     float m_run = CUDART_INF_F, s_run = 0.0f;
@@ -471,9 +498,11 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
             __syncthreads();
         } else {
             if (active) {
-                for (int q = 0; q < kp.P / 4; ++q) {
-                    const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, gi, q, s_sigma);
-                    tcol[(4 * q) * TS] = e.x; tcol[(4 * q + 1) * TS] = e.y; tcol[(4 * q + 2) * TS] = e.z; tcol[(4 * q + 3) * TS] = e.w;
+                const NoiseRow nr = noise_row<METHOD>(kp, gi);
+                float *tp = tcol;
+                for (int q = 0; q < kp.P / 4; ++q, tp += 4 * TS) {
+                    const float4 e = noise_quad<METHOD>(nr, seed, robot, tick, q, s_sigma);
+                    tp[0] = e.x; tp[TS] = e.y; tp[2 * TS] = e.z; tp[3 * TS] = e.w;
                 }
             } else {
                 for (int p = 0; p < kp.P; ++p) tcol[p * TS] = 0.0f;
@@ -484,8 +513,8 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         float cost = CUDART_INF_F;
         if (active) {
             if (ADAPTIVE) {
-                const float freq = sample_step_freq<METHOD>(kp, s.in, r, gi);
-                cost = rollout_adaptive<PARAM>(kp, s.in, tcol, freq);
+                const float freq = sample_step_freq<METHOD>(kp, s.in, seed, robot, r, gi);
+                cost = rollout_adaptive<PARAM>(kp, s.in, s.yaw, tcol, freq);
             } else {
                 cost = rollout_fixed<PARAM>(kp, s.in, s.fref, tcol);
             }
@@ -506,17 +535,17 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
             const float m_new = fminf(m_run, cmin);              // cmin is finite: the tile has >= 1 active sample
             const float scale_old = (m_run == CUDART_INF_F) ? 0.0f : expf(-(m_run - m_new));
             const float w = active ? expf(-(cost - m_new)) : 0.0f;   // exp(-(c - beta)/T), T = 1, S:828-830
-            __syncthreads();
-            s.w[t] = w;
-            const float s_tile = block_sum<TB>(w, s.red);            // barriers inside publish s.w and the tile
+            float s_tile;
+            const int nnz = compact_weights<TB>(w, t, true, s, s_tile);
             s_run = fmaf(s_run, scale_old, s_tile);
+            const float2 *wi = reinterpret_cast<const float2 *>(s.w);
             for (int p = t; p < kp.P; p += TB) {
                 const float *rowp = s.tile + p * TS;
                 float acc = 0.0f;
 #pragma unroll 4
-                for (int e = 0; e < TB; ++e) {
-                    const float we = s.w[e];
-                    if (we != 0.0f) acc = fmaf(we, rowp[e], acc);
+                for (int j = 0; j < nnz; ++j) {                  // samples whose weight underflowed to 0 add exactly nothing
+                    const float2 we = wi[j];
+                    acc = fmaf(we.x, rowp[__float_as_int(we.y)], acc);
                 }
                 s.v[p] = fmaf(s.v[p], scale_old, acc);
             }
