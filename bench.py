@@ -182,12 +182,15 @@ def _sampler_cfg(device):
                                       num_parallel_computations=N_SAMPLES, device=device)
 
 
-def make_resident_handle(device, robots, robot_base):
+def make_resident_handle(device, robots, robot_base, n_samples=None):
     """A handle with `robots` controllers whose tick packets are uploaded once and stay in HBM."""
     from quadruped_pympc_b200 import _lib, synthetic
     from quadruped_pympc_b200.sampling_mpc import make_c_config
     lib = _lib.load()
-    c = make_c_config(_sampler_cfg(device), robots)
+    scfg = _sampler_cfg(device)
+    if n_samples is not None:
+        scfg.num_parallel_computations = int(n_samples)
+    c = make_c_config(scfg, robots)
     c.robot_base = robot_base
     h = C.c_void_p()
     _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
@@ -255,6 +258,37 @@ def run_e2e(device, steps, warmup):
     return lat, 4 * ((in_floats + 3) // 4 * 4), 4 * ((out_floats + 3) // 4 * 4), int(n1.value - n0.value)
 
 
+def run_sharded(device, world, n_samples, ticks, barrier, max_over_ranks):
+    """BASELINE configs[3]: ONE controller of `n_samples` samples split over `world` GPUs.  Every rank rolls out its slice
+    and the shard records are exchanged inside the tick kernel (stores into the peers' mailboxes over NVLink, one launch
+    per rank per tick); all ranks end with the same control.  Timed through the public API with host buffers."""
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200 import synthetic
+    from quadruped_pympc_b200.distributed import make_sharded_controller
+    cfg = qp.SamplerConfig.for_robot(ROBOT, sampling_method=METHOD, control_parametrization=PARAM,
+                                     num_parallel_computations=n_samples, device=device)
+    ctrl = make_sharded_controller(cfg, exchange='peer')
+    sc = synthetic.scenario(ROBOT, GAIT, seed=0)
+    best = np.zeros(P_KNOTS, np.float32)
+    lat = np.zeros(ticks)
+    for i in range(10 + ticks):
+        if i == 10:
+            barrier()
+        ctrl.with_newkey()
+        t0 = time.perf_counter()
+        out = ctrl.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best, ctrl.master_key,
+                                   sc['phase_signal'], sc['nominal_step_freq'], 0)
+        t1 = time.perf_counter()
+        best = out[3]
+        if i >= 10:
+            lat[i - 10] = t1 - t0
+    barrier()
+    total = max_over_ranks(lat.sum())
+    return {'samples': n_samples, 'shards': world, 'exchange': 'fused in the tick kernel (NVLink peer stores), 1 launch/tick/rank',
+            'ticks': ticks, 'e2e_p50_us': float(np.percentile(lat, 50) * 1e6), 'e2e_p99_us': float(np.percentile(lat, 99) * 1e6),
+            'rollout_steps_per_s': ticks * n_samples * HORIZON / total, 'record_bytes_per_rank': 4 * (4 + P_KNOTS)}
+
+
 def measure_fp32_peak(device):
     from quadruped_pympc_b200 import _lib
     tf = C.c_float(0)
@@ -280,6 +314,9 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--robots', type=int, default=1, help='controllers per GPU in the headline measurement')
     ap.add_argument('--multi-robots', type=int, default=MULTI_ROBOTS_PER_GPU)
+    ap.add_argument('--sharded-samples', type=int, default=1000000,
+                    help='N > 1 GPUs: samples of the one large controller sharded over the ranks (0 = skip)')
+    ap.add_argument('--no-sweep', dest='sweep', action='store_false', help='skip the 1k..1M single-controller sample sweep')
     ap.add_argument('--cpu-seconds', type=float, default=10.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
@@ -365,6 +402,24 @@ def main():
                               'frac': m_tf / fp32_peak}}
         lib.qpmpc_destroy(hm)
 
+    # ---- single-controller sample sweep on one GPU (BASELINE configs[3] at 1 GPU): kernel time, inputs resident ----
+    sweep = None
+    if world == 1 and args.sweep:
+        sweep = []
+        for n in (1000, 10000, 100000, 1000000):
+            hs, keeps = make_resident_handle(local, 1, 0, n_samples=n)
+            run_resident(hs, 1, 3)
+            sms, _ = run_resident(hs, 20, 0)
+            lib.qpmpc_destroy(hs)
+            t = float(np.median(sms)) * 1e-3
+            sweep.append({'samples': n, 'kernel_us': t * 1e6, 'rollout_steps_per_s': n * HORIZON / t,
+                          'fp32_frac': n * (FLOP_PER_TICK / N_SAMPLES) / t / 1e12 / fp32_peak})
+
+    # ---- one large controller, samples sharded over the ranks (BASELINE configs[3]); fused peer exchange --------
+    sharded = None
+    if world > 1 and args.sharded_samples > 0:
+        sharded = run_sharded(local, world, args.sharded_samples, min(args.steps, 100), barrier, max_over_ranks)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = time_cpu(args.cpu_seconds)
@@ -392,6 +447,10 @@ def main():
         }
         if multi:
             line['multi_robot'] = multi
+        if sharded:
+            line['sharded_controller'] = sharded
+        if sweep:
+            line['sample_sweep'] = sweep
         if cpu:
             line['cpu_baseline'] = cpu
         print(json.dumps(line), flush=True)

@@ -118,6 +118,18 @@ class BatchedSampling_MPC:
                self._idx.copy())
         return res + (self._sig.copy(),) if cem else res
 
+    def generate_noise(self, robot: int, key=None, sigma=None) -> np.ndarray:
+        """additional_random_parameters (N,P) robot `robot` of this batch draws for `key` (parity / debugging)."""
+        h = self._ensure()
+        k = np.asarray(self.master_key if key is None else key).astype(np.uint32).ravel()
+        out = np.empty((self.num_parallel_computations, self.num_control_parameters), np.float32)
+        sg = None
+        if self.sampling_method == 'cem_mppi':
+            sg = np.ascontiguousarray(np.broadcast_to(np.asarray(
+                self.sigma_cem_mppi[robot] if sigma is None else sigma, np.float32), (self.num_control_parameters,)))
+        _lib.check(_lib.load().qpmpc_generate_noise(h, self.robot_base + int(robot), k.ctypes.data_as(_UP), _fp(sg), _fp(out)))
+        return out
+
     def fetch_costs(self, robot: int) -> np.ndarray:
         out = np.empty(self.num_parallel_computations, np.float32)
         _lib.check(_lib.load().qpmpc_get_costs(self._ensure(), int(robot), _fp(out)))

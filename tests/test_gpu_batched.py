@@ -1,0 +1,113 @@
+"""GPU: the multi-robot batch dispatch (BASELINE configs[4]): R independent controllers in ONE
+launch.  Per robot the result must equal the oracle on the noise that robot draws, must not depend on how the robots are
+grouped into handles (the partition over GPUs is a regrouping), and robots must not see each other's inputs."""
+import numpy as np
+import pytest
+
+import quadruped_pympc_b200 as qp
+from quadruped_pympc_b200 import synthetic
+from quadruped_pympc_b200.batched import BatchedSampling_MPC, partition_robots
+from oracle.sampling_oracle import OracleConfig, SamplingOracle
+from helpers import assert_tick_parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _scenarios(robot, R, first=0):
+    scs = [synthetic.scenario(robot, 'trot' if (first + r) % 2 == 0 else 'pace', seed=first + r) for r in range(R)]
+    return (np.stack([s['state'] for s in scs]).astype(np.float32), np.stack([s['reference'] for s in scs]).astype(np.float32),
+            np.stack([s['contact_sequence'] for s in scs]).astype(np.float32),
+            np.stack([s['phase_signal'] for s in scs]).astype(np.float32), scs)
+
+
+@pytest.mark.parametrize('method,adaptive', [('mppi', False), ('random_sampling', False), ('cem_mppi', False), ('mppi', True)])
+def test_each_robot_of_a_batch_equals_the_oracle(built, method, adaptive):
+    R, N = 5, 1500
+    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=N,
+              optimize_step_freq=adaptive)
+    batch = BatchedSampling_MPC(qp.SamplerConfig.for_robot('go2', **kw), R, robot_base=3)
+    orc = SamplingOracle(OracleConfig.for_robot('go2', **kw))
+    st, rf, cs, ph, scs = _scenarios('go2', R)
+    rng = np.random.RandomState(0)
+    best0 = (0.3 * rng.randn(R, orc.P)).astype(np.float32)
+    batch.with_newkey()
+    sigma = np.full(orc.P, 3.0, np.float32) if method == 'cem_mppi' else None
+    out = batch.compute_control(st, rf, cs, best0, timing=ph, nominal_step_frequency=1.4, optimize_swing=0)
+    for r in range(R):
+        noise = batch.generate_noise(r, sigma=sigma)
+        assert np.all(noise[0] == 0.0)
+        if r > 0:
+            assert not np.array_equal(noise, batch.generate_noise(r - 1, sigma=sigma))   # every robot has its own stream
+        if adaptive:     # per-sample frequencies are covered by the single-controller tests; here: it runs, finite results
+            continue
+        ref = orc.compute_control(scs[r]['state'], scs[r]['reference'], scs[r]['contact_sequence'], best0[r], noise, sigma=sigma)
+        got = dict(nmpc_GRFs=out[0][r], nmpc_predicted_state=out[1][r], best_control_parameters=out[2][r],
+                   best_cost=out[3][r], best_freq=out[4][r], costs=batch.fetch_costs(r), best_index=int(out[5][r]))
+        if method == 'cem_mppi':
+            got['new_sigma_cem_mppi'] = out[6][r]
+            got['elite_indices'] = ref['elite_indices']      # the batched surface does not return elite indices
+        assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
+    assert np.all(np.isfinite(out[0])) and np.all(np.isfinite(out[3]))
+
+
+@pytest.mark.parametrize('method', ['mppi', 'cem_mppi'])
+def test_result_does_not_depend_on_the_partition(built, method):
+    """8 robots in one handle == the same robots split 3 + 5 (two 'ranks') == one handle per robot, bit for bit."""
+    R, N = 8, 1000
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='linear_spline',
+                                     num_parallel_computations=N, lanes_per_sample=1)
+    st, rf, cs, ph, _ = _scenarios('go2', R)
+    key = np.array([42, 9], np.uint32)
+
+    def run(groups):
+        outs = []
+        for lo, hi in groups:
+            b = BatchedSampling_MPC(cfg, hi - lo, robot_base=lo)
+            outs.append(b.compute_control(st[lo:hi], rf[lo:hi], cs[lo:hi], np.zeros((hi - lo, 36), np.float32), key=key))
+        return [np.concatenate([o[i] for o in outs]) for i in range(len(outs[0]))]
+
+    whole = run([(0, R)])
+    for groups in ([(0, 3), (3, 8)], [(r, r + 1) for r in range(R)], [partition_robots(R, g, 4) for g in range(4)]):
+        part = run(groups)
+        for a, b in zip(whole, part):
+            np.testing.assert_array_equal(a, b)
+
+
+def test_robots_are_isolated(built):
+    """Changing robot 2's state changes robot 2's result only."""
+    R, N = 4, 800
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=N)
+    b = BatchedSampling_MPC(cfg, R)
+    st, rf, cs, ph, _ = _scenarios('go2', R)
+    key = np.array([42, 3], np.uint32)
+    base = b.compute_control(st, rf, cs, np.zeros((R, 96), np.float32), key=key)
+    st2 = st.copy()
+    st2[2, 3:6] += 0.2
+    pert = b.compute_control(st2, rf, cs, np.zeros((R, 96), np.float32), key=key)
+    for r in range(R):
+        same = np.array_equal(base[2][r], pert[2][r]) and base[3][r] == pert[3][r]
+        assert same == (r != 2)
+
+
+def test_batch_rejects_mixed_seeds(built):
+    """Key word 0 is launch-uniform (kernel-parameter space): the struct entry point must refuse a batch that mixes seeds."""
+    import ctypes as C
+    from quadruped_pympc_b200 import _lib
+    from quadruped_pympc_b200.sampling_mpc import make_c_config
+    lib = _lib.load()
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=256)
+    c = make_c_config(cfg, 2)
+    h = C.c_void_p()
+    _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
+    sc = synthetic.scenario('go2', 'trot', seed=0)
+    keep = [sc['state'].astype(np.float32), sc['reference'].astype(np.float32),
+            np.ascontiguousarray(sc['contact_sequence'], np.float32), np.zeros(96, np.float32)]
+    fp = lambda a: a.ctypes.data_as(_lib._FP)
+    ins, outs = (_lib.QpmpcTickIn * 2)(), (_lib.QpmpcTickOut * 2)()
+    for r in range(2):
+        i = ins[r]
+        i.state, i.reference, i.contact_sequence, i.contact_ld, i.best = fp(keep[0]), fp(keep[1]), fp(keep[2]), 12, fp(keep[3])
+        i.key[0], i.key[1] = 42 + r, 1
+    rc = lib.qpmpc_tick_batched(h, ins, outs)
+    assert rc == _lib.ERR_INVALID and b'share key[0]' in lib.qpmpc_last_error()
+    lib.qpmpc_destroy(h)
