@@ -324,6 +324,12 @@ def main():
     if args.impl == 'reference':
         return run_reference_arm(args)
 
+    # stdout carries exactly ONE line (the JSON): everything libraries print meanwhile (NCCL's version banner, ...) goes
+    # to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     rank = int(os.environ.get('RANK', '0'))
@@ -453,7 +459,8 @@ def main():
             line['sample_sweep'] = sweep
         if cpu:
             line['cpu_baseline'] = cpu
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + '\n').encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -115,7 +115,12 @@ def main():
                 f.write(json.dumps(l) + '\n')
         bad = [l for l in lines if not (l['parity_ok'] and l['ranks_bit_identical'])]
         print(f'{len(lines)} cases, {len(bad)} failed', flush=True)
-    dist.destroy_process_group()
+    dist.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    # torch's own NCCL teardown has been seen to hang after library-owned communicators (exchange = nccl) were destroyed
+    # in the same process; all results are out by now, so leave without it.
+    os._exit(0)
 
 
 if __name__ == '__main__':
