@@ -129,6 +129,26 @@ int qpmpc_num_local_samples(const qpmpc_handle *h);       /* samples evaluated b
 
 /* ---- the tick: replaces Sampling_MPC.jitted_compute_control (S:112, called at I:140/159) ------------- */
 int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
+/* The sampling-iteration loop of one MPC tick (srbd_controller_interface.py:125-168, num_sampling_iterations > 1) on the
+ * device: iteration i+1 starts from iteration i's best_control_parameters (cem_mppi: and its new sigma) with key[1] + i
+ * as the Philox counter.  `in` describes iteration 0; `out` is the last iteration's result.  All robots of the handle
+ * (R >= 1).  Equal, bit for bit, to `iterations` calls of qpmpc_tick[_batched] chained by the host. */
+int qpmpc_tick_iterations(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, qpmpc_tick_out *out);
+/* ---- Stateful controller: the whole sampling block of SRBDControllerInterface.compute_control
+ * (srbd_controller_interface.py:118-168) in one call.  best_control_parameters, sigma, the key counter and
+ * previous_contact_mpc persist in a device record between calls (initially zeros, -, key = (cfg.seed, 1),
+ * [1,1,1,1] like srbd_controller_interface.py:19).  `in[r].state` is the RAW 24-state (no foothold substitution);
+ * in[r].best / sigma / key are ignored.  Per call, on the device: prepare_state_and_reference (swing feet <- reference
+ * footholds, knots of a leg that just lifted off zeroed, centroidal_nmpc_jax.py:563-627), then `iterations` sampling
+ * iterations (with_newkey / best / with_newsigma carried; cem_mppi restarts from `sigma0` at iteration 0 like
+ * srbd_controller_interface.py:128-129), then previous_contact <- contact_sequence[:, 0].  `out` = last iteration.
+ * shift_solution is not supported here (config.py:194 default off). */
+int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, float sigma0, qpmpc_tick_out *out);
+/* (re)initialise the records: key = (seed, counter of the NEXT iteration), best (R x P) or NULL = zeros,
+ * previous_contact (R x 4) or NULL = ones */
+int qpmpc_step_reset(qpmpc_handle *h, const uint32_t key[2], const float *best, const int32_t *previous_contact);
+/* read one robot's record (any pointer may be NULL) */
+int qpmpc_step_state(qpmpc_handle *h, int robot, float *best, float *sigma, int32_t previous_contact[4], uint32_t key[2]);
 /* R robots in one launch (replaces "one process per robot", simulation/batched_simulations.py:43-58).
  * in / out are arrays of num_robots structs; parity hooks noise/step_freqs are honoured per robot. */
 int qpmpc_tick_batched(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);

@@ -149,7 +149,9 @@ struct qpmpc_handle {
     KParams partial_kp;               // noise / frequency injection state carried from shard_partial to shard_finish
     // peer exchange (fused collective of a sample-sharded controller, qpmpc_tick.cuh peer_exchange)
     float *d_mbox = nullptr;          // this rank's mailbox (cudaMalloc: exportable with cudaIpcGetMemHandle)
-    float *d_sink = nullptr;          // loopback test hook: where the records pushed to absent peers go
+    float *d_sink = nullptr;
+    float *d_ctrl = nullptr;          // stateful controller records (qpmpc_step): [R][ctrl_stride]
+    int ctrl_stride = 0;          // loopback test hook: where the records pushed to absent peers go
     float *peer_mbox[MAX_PEERS] = {}; // every rank's mailbox as seen from this device
     bool peer_ipc[MAX_PEERS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
     bool peer_attached = false;
@@ -229,7 +231,7 @@ static void free_handle(qpmpc_handle *h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
-    cudaFree(h->d_mbox); cudaFree(h->d_sink);
+    cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -407,7 +409,7 @@ extern "C" int qpmpc_shard_record_floats(const qpmpc_handle *h) { return h ? h->
 static inline float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 
-static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explicit_params) {
+static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explicit_params, bool stateful = false) {
     const KParams &kp = h->kp;
     float *rec = h->h_in + (size_t)r * kp.in_stride;
     if (!in->state || !in->reference || !in->contact_sequence) return fail(QPMPC_ERR_INVALID, "state / reference / contact_sequence must not be NULL");
@@ -418,7 +420,8 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     if (h->cfg.adaptive && !in->phase_signal) return fail(QPMPC_ERR_INVALID, "phase_signal is required by the gait-adaptive controller");
     rec[IN_NOMFREQ] = in->nominal_step_freq;
     rec[IN_OPTSWING] = u2f((uint32_t)in->optimize_swing);
-    if (r == 0) h->kp.seed = in->key[0];             // Philox key word 0 travels in kernel-parameter space (block-uniform)
+    if (stateful) { /* keys are ignored: the record holds the counter, the seed is the handle's */ }
+    else if (r == 0) h->kp.seed = in->key[0];             // Philox key word 0 travels in kernel-parameter space (block-uniform)
     else if (in->key[0] != h->kp.seed) return fail(QPMPC_ERR_INVALID, "all robots of one batch must share key[0] (robot %d differs); streams differ by robot id", r);
     rec[IN_SEED] = u2f(in->key[0]);
     rec[IN_TICK] = u2f(in->key[1]);
@@ -432,6 +435,7 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     float *best = rec + kp.off_best, *sigma = rec + kp.off_sigma;
     if (explicit_params || !in->best) memset(best, 0, h->P * sizeof(float));
     else memcpy(best, in->best, h->P * sizeof(float));
+    if (stateful) return QPMPC_OK;                    // best / sigma / key live in the device-resident record
     if (h->cfg.method == QPMPC_CEM_MPPI && !explicit_params) {
         if (!in->sigma) return fail(QPMPC_ERR_INVALID, "sigma is required by cem_mppi");
         memcpy(sigma, in->sigma, h->P * sizeof(float));
@@ -562,6 +566,130 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
         if (rc) return rc;
         if (!mapped) CK(cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
     }
+    CK(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    return QPMPC_OK;
+}
+
+// The sampling-iteration loop of one MPC tick (I:125-168) kept on the device: iteration i+1 starts from iteration i's
+// best (and, for cem_mppi, its refitted sigma) with the next Philox counter -- exactly what the interface does with
+// with_newkey() / best_control_parameters / with_newsigma() between two jitted_compute_control calls, minus the
+// D2H + H2D round trip and the host bookkeeping in between.  One H2D, `iterations` launches, one D2H.
+extern "C" int qpmpc_tick_iterations(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, qpmpc_tick_out *out) {
+    if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (iterations < 1) return fail(QPMPC_ERR_INVALID, "iterations must be >= 1");
+    if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: sampling iterations run on unsharded handles");
+    if (iterations == 1) return run_tick(h, in, out);
+    CK(cudaSetDevice(h->cfg.device));
+    const int R = h->R;
+    for (int r = 0; r < R; ++r) {
+        if (in[r].noise || in[r].step_freqs) return fail(QPMPC_ERR_INVALID, "injected noise / frequencies describe ONE iteration: use qpmpc_tick");
+        int rc = pack_one(h, r, &in[r], false);
+        if (rc) return rc;
+    }
+    KParams kp = h->kp;
+    kp.in = h->d_in; kp.out = h->d_out;                      // the carried state lives in the device copy of the packet
+    kp.carry_best = 1;
+    CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)R * kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    for (int it = 0; it < iterations; ++it) {
+        int rc = launch(h, h->tick_fn, kp, dim3(kp.nblk, R));
+        if (rc) return rc;
+    }
+    CK(cudaMemcpyAsync(h->h_out, h->d_out, (size_t)R * kp.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
+    return QPMPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Stateful controller: everything the interface keeps between ticks -- best_control_parameters,
+// sigma, the key counter, previous_contact_mpc (I:19,123-168) -- lives in a device record; one call does what the block
+// I:118-168 does: prepare_state_and_reference (in the kernel's staging), the sampling-iteration loop, the result.
+// ------------------------------------------------------------------------------------------------------
+static int ensure_ctrl(qpmpc_handle *h) {
+    if (h->d_ctrl) return QPMPC_OK;
+    h->ctrl_stride = (int)round4(2 * (size_t)h->P + 4);
+    const size_t n = (size_t)h->R * h->ctrl_stride;
+    CK(cudaMalloc((void **)&h->d_ctrl, n * sizeof(float)));
+    std::vector<float> init(n, 0.0f);
+    for (int r = 0; r < h->R; ++r) {
+        float *rec = init.data() + (size_t)r * h->ctrl_stride;
+        rec[2 * h->P] = u2f(1u);                       // master_key counter after the first with_newkey()
+        rec[2 * h->P + 1] = u2f(0xFu);                 // previous_contact_mpc = [1, 1, 1, 1], I:19
+    }
+    CK(cudaMemcpy(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    h->kp.seed = h->cfg.seed;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_step_reset(qpmpc_handle *h, const uint32_t key[2], const float *best, const int32_t *previous_contact) {
+    if (!h || !key) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = ensure_ctrl(h);
+    if (rc) return rc;
+    const size_t n = (size_t)h->R * h->ctrl_stride;
+    std::vector<float> init(n, 0.0f);
+    for (int r = 0; r < h->R; ++r) {
+        float *rec = init.data() + (size_t)r * h->ctrl_stride;
+        if (best) memcpy(rec, best + (size_t)r * h->P, (size_t)h->P * sizeof(float));
+        rec[2 * h->P] = u2f(key[1]);
+        uint32_t m = 0xFu;
+        if (previous_contact) { m = 0u; for (int l = 0; l < 4; ++l) m |= (previous_contact[4 * r + l] != 0 ? 1u : 0u) << l; }
+        rec[2 * h->P + 1] = u2f(m);
+    }
+    CK(cudaMemcpy(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    h->kp.seed = key[0];
+    h->cfg.seed = key[0];
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_step_state(qpmpc_handle *h, int robot, float *best, float *sigma, int32_t previous_contact[4], uint32_t key[2]) {
+    if (!h || robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "bad argument");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = ensure_ctrl(h);
+    if (rc) return rc;
+    std::vector<float> rec((size_t)h->ctrl_stride);
+    CK(cudaMemcpy(rec.data(), h->d_ctrl + (size_t)robot * h->ctrl_stride, rec.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    if (best) memcpy(best, rec.data(), (size_t)h->P * sizeof(float));
+    if (sigma) memcpy(sigma, rec.data() + h->P, (size_t)h->P * sizeof(float));
+    if (previous_contact) { const uint32_t m = f2u(rec[2 * h->P + 1]); for (int l = 0; l < 4; ++l) previous_contact[l] = (m >> l) & 1u; }
+    if (key) { key[0] = h->cfg.seed; key[1] = f2u(rec[2 * h->P]); }
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, float sigma0, qpmpc_tick_out *out) {
+    if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (iterations < 1) return fail(QPMPC_ERR_INVALID, "iterations must be >= 1");
+    if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: the stateful controller runs on unsharded handles");
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = ensure_ctrl(h);
+    if (rc) return rc;
+    const int R = h->R;
+    const uint32_t seed = h->cfg.seed;
+    for (int r = 0; r < R; ++r) {
+        if (in[r].noise || in[r].step_freqs) return fail(QPMPC_ERR_INVALID, "the stateful controller draws its own noise: use qpmpc_tick for injection");
+        rc = pack_one(h, r, &in[r], false, true);
+        if (rc) return rc;
+    }
+    h->kp.seed = seed;                                 // pack_one took key[0] of the (ignored) input keys
+    KParams kp = h->kp;
+    kp.ctrl_state = h->d_ctrl; kp.ctrl_stride = h->ctrl_stride; kp.sigma0 = sigma0;
+    const dim3 grid(kp.nblk, R);
+    const bool direct = h->direct;
+    if (direct) {
+        memcpy(kp.packet, h->h_in, (size_t)kp.in_stride * sizeof(float));
+        kp.param_packet = 1;
+    } else {
+        kp.in = h->d_in; kp.out = h->d_out;
+        CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)R * kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    }
+    for (int it = 0; it < iterations; ++it) {
+        kp.sigma_reset = (it == 0 && h->cfg.method == QPMPC_CEM_MPPI) ? 1 : 0;
+        if (direct && it == iterations - 1) { kp.seq = 0; return direct_tick(h, kp, grid, out); }
+        rc = launch(h, h->tick_fn, kp, grid);
+        if (rc) return rc;
+    }
+    CK(cudaMemcpyAsync(h->h_out, h->d_out, (size_t)R * kp.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
     return QPMPC_OK;

@@ -83,6 +83,12 @@ struct KParams {
     float *host_out;                        // mapped pinned host alias: [out_stride floats][stamp], or NULL
     float packet[PACKET_MAX];
     // ---- peer exchange of a sample-sharded controller (fused collective, qpmpc_tick.cuh peer_exchange) ----
+    // ---- stateful controller (qpmpc_step): best / sigma / Philox tick / previous contact live on the
+    //      device across ticks; the host uploads only state, reference, phase, frequency and the contact table ----
+    float *ctrl_state;                      // [R][ctrl_stride] = {best P, sigma P, tick u32, prev-contact mask u32, pad}, or NULL
+    int ctrl_stride;
+    int sigma_reset;                        // 1: this launch starts from sigma0 (I:128-129: reset at iteration 0 of every tick)
+    float sigma0;
     uint32_t seed;                          // Philox counter word 3 of this launch (all robots of a batch share it)
     uint32_t robot_base;                    // global robot id = robot_base + blockIdx.y (< 2^23), part of counter word 0
     int peer_world;                         // > 1: the last block pushes its shard record into every peer's mailbox over

@@ -35,8 +35,33 @@ template <int NT>
 __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Smem &s) {
     constexpr int TB = NT;
     const float *gin = kp.param_packet ? kp.packet : kp.in + (size_t)r * kp.in_stride;
-    for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
-    __syncthreads();
+    if (kp.ctrl_state == nullptr) {
+        for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
+        __syncthreads();
+    } else {
+        // Stateful controller: the packet carries what the host knows this tick (raw state, reference, phase, frequency,
+        // contact table); best, sigma, the Philox tick and the previous contact come from the device-resident record.
+        // Then the host prep of the reference, S:563-627 (prepare_state_and_reference), on the shared-memory copy:
+        const float *st = kp.ctrl_state + (size_t)r * kp.ctrl_stride;
+        for (int k = threadIdx.x; k < kp.off_best; k += TB) s.in[k] = gin[k];
+        for (int k = threadIdx.x; k < 2 * kp.P; k += TB) {
+            float v = __ldcg(st + k);
+            if (kp.sigma_reset && k >= kp.P) v = kp.sigma0;
+            s.in[kp.off_best + k] = v;
+        }
+        __syncthreads();
+        const unsigned int prev = __float_as_uint(__ldcg(st + 2 * kp.P + 1));
+        if (threadIdx.x == 0) s.in[IN_TICK] = __ldcg(st + 2 * kp.P);
+        if (threadIdx.x < 12) {                                   // swing feet <- reference footholds, S:588-595
+            const int leg = threadIdx.x / 3;
+            if (s.in[IN_CONTACT + leg * kp.H] == 0.0f) s.in[IN_STATE + 12 + threadIdx.x] = s.in[IN_REF + 12 + threadIdx.x];
+        }
+        for (int k = threadIdx.x; k < kp.P; k += TB) {            // knots of a leg that just lifted off are zeroed, S:612-625
+            const int leg = k / kp.P_leg;
+            if (((prev >> leg) & 1u) && s.in[IN_CONTACT + leg * kp.H] == 0.0f) s.in[kp.off_best + k] = 0.0f;
+        }
+        __syncthreads();
+    }
     if (threadIdx.x < kp.H) {       // gravity compensation per step, S:377-380
         const float *c = s.in + IN_CONTACT;
         const int n = threadIdx.x, H = kp.H;
@@ -238,9 +263,12 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     }
     __syncthreads();
     phase_mark(kp, 10);
+    // where the carried controller state goes: the device-resident record (stateful controller) or the resident packet
+    float *carry = kp.ctrl_state ? kp.ctrl_state + (size_t)r * kp.ctrl_stride
+                                 : (kp.carry_best ? const_cast<float *>(kp.in) + (size_t)r * kp.in_stride + kp.off_best : nullptr);
     for (int p = t; p < kp.P; p += TB) {
         out[OUT_BEST + p] = s.v[p];
-        if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + kp.off_best + p] = s.v[p];
+        if (carry) carry[p] = s.v[p];
     }
     if (t == 0) {
         tail_grf_pred<PARAM>(kp, s.in, s.yaw, s.v, out);
@@ -252,7 +280,14 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         out[OUT_BESTFREQ] = bf;
         if (METHOD != CEM_MPPI) out[OUT_NELITE] = __int_as_float(0);
         // device-resident multi-tick runs: advance the Philox counter like with_newkey() does on the host (S:498-501)
-        if (kp.carry_best) const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + IN_TICK] = __uint_as_float(tick + 1u);
+        if (kp.ctrl_state) {
+            carry[2 * kp.P] = __uint_as_float(tick + 1u);
+            unsigned int cur = 0u;                              // I:123: previous_contact_mpc = current_contact
+            for (int l = 0; l < 4; ++l) cur |= (s.in[IN_CONTACT + l * kp.H] != 0.0f ? 1u : 0u) << l;
+            carry[2 * kp.P + 1] = __uint_as_float(cur);
+        } else if (kp.carry_best) {
+            const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + IN_TICK] = __uint_as_float(tick + 1u);
+        }
     }
     if (METHOD != CEM_MPPI) return;
     // ---- CEM elite refit ----
@@ -338,6 +373,8 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
             if (ADAPTIVE) { sg = var > 3.0f ? 3.0f : var; sg = sg < 0.5f ? 0.5f : sg; }      // A:1118-1121 (no sqrt)
             else { sg = sqrtf(var); sg = sg > 5.0f ? 5.0f : sg; sg = sg < 0.2f ? 0.2f : sg; } // S:1079-1081
             out[kp.off_out_sigma + p] = sg;
+            // device-resident sampling iterations (I:125-148): the next iteration draws with the refitted sigma
+            if (carry) carry[kp.P + p] = sg;
         }
     }
 }

@@ -188,6 +188,7 @@ class Sampling_MPC:
         self.adaptive = bool(cfg.optimize_step_freq)
         self.elite_k = (cfg.elite_k or (200 if self.adaptive else 10)) if cfg.sampling_method == 'cem_mppi' else 0
         self._shard = (int(shard_rank), int(shard_world))
+        self._stateful = False
         self._handle = None
         self._pid = None
         self._buf = None
@@ -206,6 +207,7 @@ class Sampling_MPC:
         h = C.c_void_p()
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
+        self._stateful = False                                  # a new handle starts without a device record
         self._n_local = lib.qpmpc_num_local_samples(h)
         self._buf = _TickBuffers(self.num_control_parameters, self.elite_k, self.horizon)
         return h
@@ -379,7 +381,7 @@ class Sampling_MPC:
 
     # ------------------------------------------------------------------ the tick
     def compute_control(self, state, reference, contact_sequence, best_control_parameters, key, *args,
-                        noise=None, step_freqs=None, **kwargs):
+                        noise=None, step_freqs=None, iterations=1, **kwargs):
         """One MPC tick = `jitted_compute_control` of the reference.
 
         random_sampling / mppi (S:629-932, A:629-962):
@@ -414,11 +416,94 @@ class Sampling_MPC:
             raise TypeError('the gait-adaptive controller needs timing, nominal_step_frequency and optimize_swing '
                             '(A:326,637-638,972-974)')
         out = self._tick(state, reference, contact_sequence, best_control_parameters, key, sigma, timing, nominal,
-                         optimize_swing, noise, step_freqs)
+                         optimize_swing, noise, step_freqs, iterations)
         return out
 
+    def compute_control_iterations(self, state, reference, contact_sequence, best_control_parameters, key, *args,
+                                   iterations=None, **kwargs):
+        """The sampling-iteration loop of one MPC tick (I:125-168) in ONE call, state carried on the device:
+
+            for _ in range(num_sampling_iterations):
+                controller = controller.with_newkey()
+                ... = controller.jitted_compute_control(state, ref, contact_sequence, controller.best_control_parameters,
+                                                        controller.master_key, [controller.sigma_cem_mppi,] ...)
+                controller.best_control_parameters = best ; controller = controller.with_newsigma(new_sigma)
+
+        `key` is the key of the FIRST iteration (call `with_newkey()` once before, as the loop does); iteration i draws
+        with `key[1] + i`.  Returns the last iteration's tuple, bit-identical to the loop; `master_key` is advanced by
+        `iterations - 1` so that the next `with_newkey()` continues the sequence."""
+        n = self.num_sampling_iterations if iterations is None else int(iterations)
+        out = self.compute_control(state, reference, contact_sequence, best_control_parameters, key, *args,
+                                   iterations=n, **kwargs)
+        k = np.asarray(key).astype(np.uint32).ravel()
+        self.master_key = np.array([k[0], (int(k[1]) + n - 1) & 0xFFFFFFFF], dtype=np.uint32)
+        return out
+
+    # ------------------------------------------------------------------ stateful controller (SURVEY 8f rank 1)
+    _STATE_KEYS = ("position", "linear_velocity", "orientation", "angular_velocity", "foot_FL", "foot_FR", "foot_RL", "foot_RR")
+    _REF_KEYS = ("ref_position", "ref_linear_velocity", "ref_orientation", "ref_angular_velocity",
+                 "ref_foot_FL", "ref_foot_FR", "ref_foot_RL", "ref_foot_RR")
+
+    def step(self, state_current, ref_state, contact_sequence, pgg_phase_signal=None, pgg_step_freq=None,
+             optimize_swing=0, iterations=None):
+        """The sampling block of SRBDControllerInterface.compute_control (I:118-168) in ONE call:
+
+            prepare_state_and_reference(...); previous_contact_mpc = current_contact
+            for _ in range(num_sampling_iterations): with_newkey(); [with_newsigma(cfg sigma) at 0]; jitted_compute_control(...)
+
+        with best_control_parameters, sigma, the key counter and previous_contact_mpc kept in a device record between
+        calls (the foothold substitution and the lift-off knot zeroing happen in the kernel's staging).  `state_current`
+        / `ref_state` are the interface's dicts (or raw 24-vectors).  Returns the last iteration's tuple; the host
+        mirrors (`best_control_parameters`, `master_key`, `sigma_cem_mppi`) are kept in step."""
+        if self.cfg.shift_solution:
+            raise _lib.QpmpcError(_lib.ERR_INVALID, 'step(): shift_solution is not supported by the stateful controller')
+        h, lib, b = self._ensure(), _lib.load(), self._buf
+        n = self.num_sampling_iterations if iterations is None else int(iterations)
+        if isinstance(state_current, dict):
+            st = np.concatenate([np.asarray(state_current[k], np.float64).reshape(-1) for k in self._STATE_KEYS])
+        else:
+            st = np.asarray(state_current).reshape(24)
+        if isinstance(ref_state, dict):
+            rf = np.concatenate([np.asarray(ref_state[k], np.float64).reshape(-1)[:3] for k in self._REF_KEYS])
+        else:
+            rf = np.asarray(ref_state).reshape(24)
+        if not self._stateful:
+            key = (C.c_uint32 * 2)(int(self.master_key[0]), (int(self.master_key[1]) + 1) & 0xFFFFFFFF)
+            best = _f32(self.best_control_parameters, (self.num_control_parameters,))
+            _lib.check(lib.qpmpc_step_reset(h, key, _fp(best), None))
+            self._stateful = True
+        b.fill(st, rf, contact_sequence, 0.0, (0, 0), None, pgg_phase_signal, pgg_step_freq, optimize_swing, None, None,
+               self.horizon)
+        self._tick_serial += 1
+        _lib.check(lib.qpmpc_step(h, C.byref(b.cin), n, float(self.cfg.sigma_cem_mppi), C.byref(b.cout)))
+        out = self._unpack(b)
+        self.best_control_parameters = out[3]
+        self.master_key = np.array([self.master_key[0], (int(self.master_key[1]) + n) & 0xFFFFFFFF], dtype=np.uint32)
+        if self._cem:
+            self.sigma_cem_mppi = out[7]
+        return out
+
+    def step_reset(self, previous_contact=(1, 1, 1, 1)):
+        """Restart the stateful controller from the host mirrors (`best_control_parameters`, `master_key`)."""
+        h = self._ensure()
+        key = (C.c_uint32 * 2)(int(self.master_key[0]), (int(self.master_key[1]) + 1) & 0xFFFFFFFF)
+        pc = (C.c_int32 * 4)(*[int(x) for x in previous_contact])
+        best = _f32(self.best_control_parameters, (self.num_control_parameters,))
+        _lib.check(_lib.load().qpmpc_step_reset(h, key, _fp(best), pc))
+        self._stateful = True
+        return self
+
+    def step_state(self):
+        """(best, sigma, previous_contact, key of the next iteration) as stored on the device."""
+        h = self._ensure()
+        P = self.num_control_parameters
+        best, sigma = np.zeros(P, np.float32), np.zeros(P, np.float32)
+        pc, key = (C.c_int32 * 4)(), (C.c_uint32 * 2)()
+        _lib.check(_lib.load().qpmpc_step_state(h, 0, _fp(best), _fp(sigma), pc, key))
+        return best, sigma, np.array(pc[:]), np.array(key[:], np.uint32)
+
     def _tick(self, state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing, noise,
-              step_freqs):
+              step_freqs, iterations=1):
         h = self._ensure()
         lib = _lib.load()
         b = self._buf
@@ -433,7 +518,9 @@ class Sampling_MPC:
         b.fill(state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing, noise, step_freqs,
                self.horizon)
         self._tick_serial += 1
-        if self._shard[1] == 1:
+        if iterations != 1:
+            _lib.check(lib.qpmpc_tick_iterations(h, C.byref(b.cin), int(iterations), C.byref(b.cout)))
+        elif self._shard[1] == 1:
             _lib.check(lib.qpmpc_tick(h, C.byref(b.cin), C.byref(b.cout)))
         else:
             _lib.check(lib.qpmpc_tick_sharded(h, C.byref(b.cin), C.byref(b.cout)))

@@ -111,3 +111,44 @@ def test_batch_rejects_mixed_seeds(built):
     rc = lib.qpmpc_tick_batched(h, ins, outs)
     assert rc == _lib.ERR_INVALID and b'share key[0]' in lib.qpmpc_last_error()
     lib.qpmpc_destroy(h)
+
+
+@pytest.mark.parametrize('method,iters', [('mppi', 2), ('cem_mppi', 2), ('random_sampling', 1)])
+def test_stateful_batch_step_equals_per_robot_host_loops(built, method, iters):
+    """`BatchedSampling_MPC.step` (device-resident per-robot state, prep in the kernel) against one host-driven
+    interface block per robot (single-robot batches with the same robot id), over ticks with contact changes."""
+    R, N = 3, 1200
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='cubic_spline',
+                                     num_parallel_computations=N, lanes_per_sample=1)
+    dev = BatchedSampling_MPC(cfg, R, robot_base=4)
+    hosts = [BatchedSampling_MPC(cfg, 1, robot_base=4 + r) for r in range(R)]
+    prev = np.ones((R, 4))
+    P = dev.num_control_parameters
+    cem = method == 'cem_mppi'
+    for tick in range(4):
+        scs = [synthetic.scenario('go2', 'trot', seed=50 + r, sim_steps=40 * tick + 13 * r) for r in range(R)]
+        st = np.stack([s['state'] for s in scs]).astype(np.float32)
+        rf = np.stack([s['reference'] for s in scs]).astype(np.float32)
+        rf[:, 12:] += 0.02                                            # reference footholds differ from the feet
+        cs = np.stack([s['contact_sequence'] for s in scs]).astype(np.float32)
+        out_d = dev.step(st, rf, cs, iterations=iters)
+        for r, hc in enumerate(hosts):
+            cur = cs[r, :, 0]
+            s_r = st[r].copy()
+            for leg in range(4):                                       # S:588-595, S:612-625 on the host
+                if cur[leg] == 0.0:
+                    s_r[12 + 3 * leg:15 + 3 * leg] = rf[r, 12 + 3 * leg:15 + 3 * leg]
+                if prev[r, leg] == 1 and cur[leg] == 0:
+                    hc.best_control_parameters[0, leg * (P // 4):(leg + 1) * (P // 4)] = 0.0
+            prev[r] = cur
+            for it in range(iters):
+                hc.with_newkey()
+                sg = np.full((1, P), cfg.sigma_cem_mppi, np.float32) if (cem and it == 0) else hc.sigma_cem_mppi
+                o = hc.compute_control(s_r[None], rf[r][None], cs[r][None], hc.best_control_parameters, sigma=sg)
+                hc.best_control_parameters = o[2]
+                if cem:
+                    hc.sigma_cem_mppi = o[6]
+            for k in range(6):
+                np.testing.assert_array_equal(out_d[k][r], o[k][0])
+            if cem:
+                np.testing.assert_array_equal(out_d[6][r], o[6][0])

@@ -78,3 +78,91 @@ def test_interface_tick_loop(built, method):
                 sigma_ref = np.asarray(sigma_cem_mppi, np.float32).copy()
         assert np.array(nmpc_GRFs).shape == (12,) and nmpc_footholds.shape == (12,)
         assert np.all(np.array(nmpc_GRFs).reshape(4, 3)[current_contact == 0] == 0)
+
+
+@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('method,adaptive', [('random_sampling', False), ('mppi', False), ('cem_mppi', False),
+                                             ('mppi', True), ('cem_mppi', True)])
+def test_device_resident_sampling_iterations_equal_the_host_loop(built, method, adaptive, lanes):
+    """the loop I:125-168 (with_newkey / best / with_newsigma between iterations) in one call with the
+    state carried on the device must equal the loop driven from the host, bit for bit."""
+    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=3000,
+              num_sampling_iterations=4, optimize_step_freq=adaptive, lanes_per_sample=lanes)
+    sc = synthetic.scenario('go2', 'trot', seed=21)
+    cem = method == 'cem_mppi'
+    tail = (sc['phase_signal'], sc['nominal_step_freq'], 1)
+
+    host = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
+    best = np.zeros(host.num_control_parameters, np.float32)
+    host.with_newsigma(3)
+    for _ in range(host.num_sampling_iterations):
+        host.with_newkey()
+        args = ((host.sigma_cem_mppi,) if cem else ()) + tail
+        out_h = host.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best, host.master_key, *args)
+        best = out_h[3]
+        if cem:
+            host.with_newsigma(out_h[7])
+
+    dev = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
+    dev.with_newsigma(3)
+    dev.with_newkey()
+    args = ((dev.sigma_cem_mppi,) if cem else ()) + tail
+    out_d = dev.compute_control_iterations(sc['state'], sc['reference'], sc['contact_sequence'],
+                                           np.zeros(dev.num_control_parameters, np.float32), dev.master_key, *args)
+    for a, b in zip(out_h[:6], out_d[:6]):
+        np.testing.assert_array_equal(np.asarray(a), np.asarray(b))
+    np.testing.assert_array_equal(np.asarray(out_h[6]), np.asarray(out_d[6]))      # costs of the last iteration
+    if cem:
+        np.testing.assert_array_equal(out_h[7], out_d[7])
+    np.testing.assert_array_equal(host.master_key, dev.master_key)
+    assert host.last_best_index == dev.last_best_index
+
+
+@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('method,adaptive,iters', [('random_sampling', False, 1), ('mppi', False, 3), ('cem_mppi', False, 2),
+                                                   ('mppi', True, 2), ('cem_mppi', True, 1)])
+def test_stateful_step_equals_the_interface_block(built, method, adaptive, iters, lanes):
+    """`step()` (device-resident best / sigma / key counter / previous contact, host prep done in the
+    kernel's staging) against the block I:118-168 driven from the host with the same class, over ticks that contain
+    lift-offs and touch-downs.  Must agree bit for bit, including the carried state."""
+    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=2500,
+              num_sampling_iterations=iters, optimize_step_freq=adaptive, lanes_per_sample=lanes)
+    cem = method == 'cem_mppi'
+    host = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
+    dev = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
+    previous_contact_mpc = np.array([1, 1, 1, 1])
+    saw_liftoff = False
+    for tick in range(6):
+        sc = synthetic.scenario('go2', 'trot', seed=30 + tick, sim_steps=45 * tick)
+        state_current, ref_state = _dicts(sc)
+        for k in ('ref_foot_FL', 'ref_foot_FR', 'ref_foot_RL', 'ref_foot_RR'):      # footholds differ from the feet
+            ref_state[k] = ref_state[k] + 0.01 * (tick + 1)
+        contact_sequence = sc['contact_sequence']
+        current_contact = contact_sequence[:, 0].copy()
+        saw_liftoff |= bool(np.any((previous_contact_mpc == 1) & (current_contact == 0)))
+        # ---- host-driven block, I:118-168
+        state_jax, ref_jax = host.prepare_state_and_reference(state_current, ref_state, current_contact, previous_contact_mpc)
+        previous_contact_mpc = current_contact
+        for it in range(host.num_sampling_iterations):
+            host.with_newkey()
+            if cem and it == 0:
+                host.with_newsigma(host.cfg.sigma_cem_mppi)
+            tail = (sc['phase_signal'], sc['nominal_step_freq'], 1)
+            args = ((host.sigma_cem_mppi,) if cem else ()) + tail
+            out_h = host.jitted_compute_control(state_jax, ref_jax, contact_sequence, host.best_control_parameters,
+                                                host.master_key, *args)
+            host.best_control_parameters = out_h[3]
+            if cem:
+                host.with_newsigma(out_h[7])
+        # ---- the same block in one call
+        out_d = dev.step(state_current, ref_state, contact_sequence, sc['phase_signal'], sc['nominal_step_freq'], 1)
+        for a, b in zip(out_h[:6], out_d[:6]):
+            np.testing.assert_array_equal(np.asarray(a), np.asarray(b))
+        if cem:
+            np.testing.assert_array_equal(out_h[7], out_d[7])
+        np.testing.assert_array_equal(host.master_key, dev.master_key)
+        best, sigma, pc, key = dev.step_state()
+        np.testing.assert_array_equal(best, out_h[3])
+        np.testing.assert_array_equal(pc, current_contact.astype(int))
+        assert key[1] == host.master_key[1] + 1
+    assert saw_liftoff
