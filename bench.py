@@ -309,8 +309,8 @@ def ncu_traffic_bytes():
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=200)
-    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--steps', type=int, default=1000)   # p50 / p99 over >= 1000 ticks
+    ap.add_argument('--warmup', type=int, default=50)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--robots', type=int, default=1, help='controllers per GPU in the headline measurement')
     ap.add_argument('--multi-robots', type=int, default=MULTI_ROBOTS_PER_GPU)
