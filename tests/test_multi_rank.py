@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from quadruped_pympc_b200.distributed import partition_robots, shard_slice, broadcast_bytes
+from quadruped_pympc_b200.distributed import partition_robots, shard_slice, broadcast_bytes, all_gather_bytes
 
 
 def _free_port():
@@ -29,6 +29,9 @@ def _worker(rank, world, port, R, N, out):
         dist.all_gather(allr, mine)
         payload = bytes(range(128)) if rank == 0 else None
         got = broadcast_bytes(payload, 128, 0)
+        # hand-out of the peer-exchange mailbox descriptors: every rank contributes 128 bytes, all get them in rank order
+        blobs = all_gather_bytes(bytes([rank]) * 128)
+        assert blobs == [bytes([r]) * 128 for r in range(world)]
         # robots partition with no communication: each rank reports only a count (ticks/s is summed by the launcher)
         ticks = torch.tensor([float(hi - lo)])
         dist.all_reduce(ticks)
