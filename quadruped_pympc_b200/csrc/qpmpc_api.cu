@@ -19,7 +19,7 @@ using namespace qp;
 
 // samples per launch (all robots) up to which the four-lanes-per-sample kernel is chosen automatically (measured
 // crossover on B200)
-static const long long QPMPC_QUAD_MAX_SAMPLES = 24576;
+static const long long QPMPC_QUAD_MAX_SAMPLES = 6144;    // r1g sweep: 4k -> quad 22.6 vs 24.1 us, 10k -> 26.7 vs 24.6 us
 
 // ------------------------------------------------------------------------------------------------------
 // error plumbing

@@ -176,9 +176,18 @@ __device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
 }
 
 template <int METHOD>
+__device__ __forceinline__ float4 noise_quad_nz(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
+                                                const float *s_sigma);
+template <int METHOD>
 __device__ __forceinline__ float4 noise_quad(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
                                              const float *s_sigma) {
     if (nr.zero) return make_float4(0.f, 0.f, 0.f, 0.f);
+    return noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
+}
+// rows >= 1 (the caller has dealt with the all-zero row 0 outside its loop over quads)
+template <int METHOD>
+__device__ __forceinline__ float4 noise_quad_nz(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
+                                                const float *s_sigma) {
     uint4 r = philox4x32_10((uint32_t)q | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
     float4 v;
     if (METHOD == RANDOM_SAMPLING && nr.seg == 2) {
@@ -353,8 +362,8 @@ __device__ __forceinline__ void add_leg(const KParams &kp, const Body &b, const 
 template <int PARAM>
 __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s_in, const float *s_fref, const float *tcol) {
     const float *s_yaw = s_fref + MAX_H;
+    const int *s_cmask = reinterpret_cast<const int *>(s_fref + MAX_H + 4);   // stance mask per step (stage_inputs)
     const float *s_best = s_in + kp.off_best;
-    const float *s_contact = s_in + IN_CONTACT;
     const float *ref = s_in + IN_REF;
     const float *feet = s_in + IN_STATE + 12;
     Body b = load_body(s_in + IN_STATE);
@@ -394,9 +403,10 @@ __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s
         const float fref = s_fref[n];
         float Fx = 0.f, Fy = 0.f, Fz = 0.f, tx = 0.f, ty = 0.f, tz = 0.f;
 #pragma unroll
+        const int cm = s_cmask[n];
+#pragma unroll
         for (int l = 0; l < 4; ++l) {
-            const float c = s_contact[l * H + n];
-            if (c != 0.0f) {
+            if (cm & (1 << l)) {
                 float fx, fy, fz;
                 if (PARAM == CUBIC) {
                     fx = w0 * ka[l][0] + w1 * kb[l][0] + w2 * kc[l][0] + w3 * kd[l][0];

@@ -225,10 +225,11 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             }
             __syncthreads();
         } else {
-            if (active) {
+            if (active && gi != 0) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
+#pragma unroll 2
                 for (int q = q_lo; q < q_hi; ++q) {
-                    const float4 e = noise_quad<METHOD>(nr, seed, robot, tick, q, s_sigma);
+                    const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
                     tcol[(4 * q) * QTS] = e.x; tcol[(4 * q + 1) * QTS] = e.y; tcol[(4 * q + 2) * QTS] = e.z; tcol[(4 * q + 3) * QTS] = e.w;
                 }
             } else {

@@ -12,12 +12,14 @@ constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogra
 // shared-memory carve-up (float offsets); every region starts 16-byte aligned
 struct Smem {
     float *in, *fref, *yaw, *w, *v, *red, *tile;
+    int *cmask;
     int *idx;                               // MAX_ELITE elite indices (CEM refit)
     __device__ Smem(float *base, const KParams &kp, int nt = TB) {
         in = base;
         fref = in + kp.in_stride;
         yaw = fref + MAX_H;                 // {yaw0, sin yaw0, cos yaw0, -}: directly behind fref (rollouts rely on it)
-        w = yaw + 4;                        // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
+        cmask = reinterpret_cast<int *>(yaw + 4);   // stance mask per step (bit l = leg l), directly behind yaw
+        w = yaw + 4 + MAX_H;                        // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
         v = w + 2 * nt;
         red = v + kp.P;
         idx = reinterpret_cast<int *>(red + 16);
@@ -28,7 +30,7 @@ struct Smem {
 // the CEM elite refit, nt / 4 + 1 for the four-lanes-per-sample kernel without CEM)
 __host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB, int tile_cols = TS) {
     const size_t tile = (size_t)P * tile_cols > (size_t)SCRATCH_FLOATS ? (size_t)P * tile_cols : (size_t)SCRATCH_FLOATS;
-    return (size_t)in_stride + MAX_H + 4 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
+    return (size_t)in_stride + 2 * MAX_H + 4 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
 }
 
 template <int NT>
@@ -67,6 +69,7 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
         const int n = threadIdx.x, H = kp.H;
         const float nst = ((c[n] + c[H + n]) + c[2 * H + n]) + c[3 * H + n];
         s.fref[n] = kp.mg / nst;
+        s.cmask[n] = (c[n] != 0.0f ? 1 : 0) | (c[H + n] != 0.0f ? 2 : 0) | (c[2 * H + n] != 0.0f ? 4 : 0) | (c[3 * H + n] != 0.0f ? 8 : 0);
     }
     if (threadIdx.x == TB - 1) {    // block-uniform yaw0 and its sine / cosine (sincos_yaw)
         const float y0 = s.in[IN_STATE + 8];
@@ -534,14 +537,15 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
             }
             __syncthreads();
         } else {
-            if (active) {
+            if (active && gi != 0) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
                 float *tp = tcol;
+#pragma unroll 2
                 for (int q = 0; q < kp.P / 4; ++q, tp += 4 * TS) {
-                    const float4 e = noise_quad<METHOD>(nr, seed, robot, tick, q, s_sigma);
+                    const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
                     tp[0] = e.x; tp[TS] = e.y; tp[2 * TS] = e.z; tp[3 * TS] = e.w;
                 }
-            } else {
+            } else {                                            // padding rows and row 0 (the previous best re-evaluated)
                 for (int p = 0; p < kp.P; ++p) tcol[p * TS] = 0.0f;
             }
         }
