@@ -141,7 +141,18 @@ def time_cpu(seconds_budget, min_ticks=3, max_ticks=100000, warmup=2):
         tick(warmup + n)
         n += 1
     dt = time.perf_counter() - t0
+    # the same port on ONE core (SURVEY 8d ii): a few ticks are enough, a tick takes ~threads x longer
+    from oracle import c_oracle
+    c_oracle.set_num_threads(1)
+    t1 = time.perf_counter()
+    n1 = 0
+    while n1 < 3 or (time.perf_counter() - t1 < 0.15 * seconds_budget and n1 < 50):
+        tick(warmup + n + n1)
+        n1 += 1
+    dt1 = time.perf_counter() - t1
+    c_oracle.set_num_threads(threads)
     return {'value': n * N_SAMPLES * HORIZON / dt, 'unit': 'rollout-steps/s', 'cores': threads, 'kind': 'port',
+            'single_core_value': n1 * N_SAMPLES * HORIZON / dt1,
             'sample': f'{n} full ticks of the same workload (noise draw + {N_SAMPLES} rollouts x H={HORIZON} + MPPI update) '
                       f'in {dt:.2f} s, C/OpenMP port of the reference tick (oracle/sampling_oracle.c), {threads} threads',
             'ms_per_tick': 1e3 * dt / n}

@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
             if (active && gi != 0) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
                 float *tp = tcol;
-#pragma unroll 2
+#pragma unroll 4
                 for (int q = 0; q < kp.P / 4; ++q, tp += 4 * TS) {
                     const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
                     tp[0] = e.x; tp[TS] = e.y; tp[2 * TS] = e.z; tp[3 * TS] = e.w;
