@@ -300,6 +300,40 @@ def run_sharded(device, world, n_samples, ticks, barrier, max_over_ranks):
             'rollout_steps_per_s': ticks * n_samples * HORIZON / total, 'record_bytes_per_rank': 4 * (4 + P_KNOTS)}
 
 
+def run_multi_e2e(device, robots, robot_base, ticks, barrier, max_over_ranks, world):
+    """The batched dispatch through its public API with HOST arrays (BatchedSampling_MPC.compute_control ->
+    qpmpc_tick_batched_flat): per tick R packets are packed, copied H2D, one launch, R result packets D2H."""
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200 import synthetic
+    from quadruped_pympc_b200.batched import BatchedSampling_MPC
+    ctrl = BatchedSampling_MPC(_sampler_cfg(device), robots, robot_base=robot_base)
+    scs = [synthetic.scenario(ROBOT, GAIT, seed=robot_base + r) for r in range(robots)]
+    st = np.stack([s['state'] for s in scs]).astype(np.float32)
+    rf = np.stack([s['reference'] for s in scs]).astype(np.float32)
+    cs = np.stack([s['contact_sequence'] for s in scs]).astype(np.float32)
+    best = np.zeros((robots, P_KNOTS), np.float32)
+    lat = np.zeros(ticks)
+    for i in range(3 + ticks):
+        if i == 3:
+            barrier()
+        ctrl.with_newkey()
+        t0 = time.perf_counter()
+        out = ctrl.compute_control(st, rf, cs, best)
+        t1 = time.perf_counter()
+        best = out[2]
+        if i >= 3:
+            lat[i - 3] = t1 - t0
+    barrier()
+    total = max_over_ranks(lat.sum())
+    ctrl.close()
+    in_floats, out_floats = 60 + 4 * HORIZON + 2 * P_KNOTS, 40 + 2 * P_KNOTS
+    return {'e2e_ms_per_batched_tick': float(np.median(lat) * 1e3),
+            'e2e_robot_ticks_per_s': world * robots * ticks / total,
+            'e2e_rollout_steps_per_s': world * robots * N_SAMPLES * HORIZON * ticks / total,
+            'e2e_h2d_bytes_per_tick': 4 * in_floats * robots, 'e2e_d2h_bytes_per_tick': 4 * out_floats * robots,
+            'e2e_api': 'BatchedSampling_MPC.compute_control -> qpmpc_tick_batched_flat (host arrays)'}
+
+
 def measure_fp32_peak(device):
     from quadruped_pympc_b200 import _lib
     tf = C.c_float(0)
@@ -418,6 +452,7 @@ def main():
                  'roofline': {'bound': 'fp32', 'achieved': m_tf, 'peak': fp32_peak, 'unit': 'TFLOP/s',
                               'frac': m_tf / fp32_peak}}
         lib.qpmpc_destroy(hm)
+        multi.update(run_multi_e2e(local, MR, rank * MR, msteps, barrier, max_over_ranks, world))
 
     # ---- single-controller sample sweep on one GPU (BASELINE configs[3] at 1 GPU): kernel time, inputs resident ----
     sweep = None

@@ -161,6 +161,12 @@ int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, const float *r
                             const float *nominal_step_freqs, const int32_t *optimize_swing, const uint32_t key[2],
                             float *grfs, float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
                             int32_t *best_indices, float *sigma_new);
+/* qpmpc_step for R robots in flat arrays (states RAW, R x 24; outputs like qpmpc_tick_batched_flat) */
+int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float *references, const float *contacts,
+                    int32_t contact_ld, const float *phase_signals, const float *nominal_step_freqs,
+                    const int32_t *optimize_swing, int32_t iterations, float sigma0, float *grfs,
+                    float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
+                    int32_t *best_indices, float *sigma_new);
 /* costs (N) of the last tick of robot r, fetched lazily (the interface ignores them, I:138,158) */
 int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst);
 

@@ -66,7 +66,7 @@ class QpmpcTickOut(C.Structure):
 # every symbol include/qpmpc.h declares (tests check the header and this list against the built library)
 EXPORTS = [
     'qpmpc_abi_version', 'qpmpc_last_error', 'qpmpc_device_count', 'qpmpc_config_defaults', 'qpmpc_create',
-    'qpmpc_destroy', 'qpmpc_num_parameters', 'qpmpc_num_local_samples', 'qpmpc_tick', 'qpmpc_tick_iterations', 'qpmpc_step', 'qpmpc_step_reset',
+    'qpmpc_destroy', 'qpmpc_num_parameters', 'qpmpc_num_local_samples', 'qpmpc_tick', 'qpmpc_tick_iterations', 'qpmpc_step', 'qpmpc_step_flat', 'qpmpc_step_reset',
     'qpmpc_step_state', 'qpmpc_tick_batched',
     'qpmpc_tick_batched_flat',
     'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
@@ -138,10 +138,12 @@ def load():
     lib.qpmpc_tick.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
     lib.qpmpc_tick_iterations.argtypes = [H, C.POINTER(QpmpcTickIn), C.c_int32, C.POINTER(QpmpcTickOut)]
     lib.qpmpc_step.argtypes = [H, C.POINTER(QpmpcTickIn), C.c_int32, C.c_float, C.POINTER(QpmpcTickOut)]
+    _IP, _UP = C.POINTER(C.c_int32), C.POINTER(C.c_uint32)
+    lib.qpmpc_step_flat.argtypes = [H, _FP, _FP, _FP, C.c_int32, _FP, _FP, _IP, C.c_int32, C.c_float,
+                                    _FP, _FP, _FP, _FP, _FP, _IP, _FP]
     lib.qpmpc_step_reset.argtypes = [H, C.POINTER(C.c_uint32), _FP, C.POINTER(C.c_int32)]
     lib.qpmpc_step_state.argtypes = [H, C.c_int, _FP, _FP, C.POINTER(C.c_int32), C.POINTER(C.c_uint32)]
     lib.qpmpc_tick_batched.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
-    _IP, _UP = C.POINTER(C.c_int32), C.POINTER(C.c_uint32)
     lib.qpmpc_tick_batched_flat.argtypes = [H, _FP, _FP, _FP, C.c_int32, _FP, _FP, _FP, _FP, _IP, _UP,
                                             _FP, _FP, _FP, _FP, _FP, _IP, _FP]
     lib.qpmpc_get_costs.argtypes = [H, C.c_int, _FP]

@@ -67,6 +67,7 @@ class BatchedSampling_MPC:
         h = C.c_void_p()
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
+        self._stateful = False
         return h
 
     def close(self):
@@ -119,21 +120,6 @@ class BatchedSampling_MPC:
         return res + (self._sig.copy(),) if cem else res
 
     # ------------------------------------------------------------------ stateful batch
-    def _bind_step(self):
-        """ctypes structs bound ONCE to rows of persistent staging arrays (no marshalling on the tick path)."""
-        R, P, H = self.num_robots, self.num_control_parameters, self.horizon
-        self._s_state, self._s_ref = np.zeros((R, 24), np.float32), np.zeros((R, 24), np.float32)
-        self._s_contact, self._s_timing = np.zeros((R, 4, H), np.float32), np.zeros((R, 4), np.float32)
-        self._s_in, self._s_out = (_lib.QpmpcTickIn * R)(), (_lib.QpmpcTickOut * R)()
-        F = C.POINTER(C.c_float)
-        row = lambda a, r: C.cast(a.ctypes.data + r * a.strides[0], F)
-        for r in range(R):
-            i, o = self._s_in[r], self._s_out[r]
-            i.state, i.reference, i.contact_sequence, i.contact_ld = row(self._s_state, r), row(self._s_ref, r), row(self._s_contact, r), H
-            i.phase_signal = row(self._s_timing, r)
-            o.best, o.sigma_new = row(self._best, r), row(self._sig, r)
-        self._s_bound = True
-
     def step(self, states, references, contact_sequences, timing=None, nominal_step_frequency=None, optimize_swing=None,
              iterations=1):
         """The sampling block of SRBDControllerInterface.compute_control (I:118-168) for all R robots in one call, with
@@ -141,37 +127,34 @@ class BatchedSampling_MPC:
         (foothold substitution and lift-off zeroing happen in the kernel), `iterations` sampling iterations.
         states (R,24) RAW, references (R,24), contact_sequences (R,4,>=H) -> like compute_control."""
         h = self._ensure()
-        R, H = self.num_robots, self.horizon
-        if not getattr(self, '_s_bound', False):
-            self._bind_step()
+        lib = _lib.load()
+        R, P, H = self.num_robots, self.num_control_parameters, self.horizon
+        if not getattr(self, '_stateful', False):
             key = (C.c_uint32 * 2)(int(self.master_key[0]), (int(self.master_key[1]) + 1) & 0xFFFFFFFF)
-            _lib.check(_lib.load().qpmpc_step_reset(h, key, _fp(_f32(self.best_control_parameters, (R, self.num_control_parameters))), None))
-        cs = np.asarray(contact_sequences)
+            _lib.check(lib.qpmpc_step_reset(h, key, _fp(_f32(self.best_control_parameters, (R, P))), None))
+            self._stateful = True
+        st, rf = _f32(states, (R, 24)), _f32(references, (R, 24))
+        cs = _f32(contact_sequences)
         if cs.ndim != 3 or cs.shape[0] != R or cs.shape[1] != 4 or cs.shape[2] < H:
             raise _lib.QpmpcError(_lib.ERR_INVALID, f'contact_sequences must be ({R}, 4, >= {H}), got {cs.shape}')
-        self._s_state[...] = np.asarray(states).reshape(R, 24)
-        self._s_ref[...] = np.asarray(references).reshape(R, 24)
-        self._s_contact[...] = cs[:, :, :H]
-        if timing is not None:
-            self._s_timing[...] = timing
-        elif self.adaptive:
+        tm = _f32(timing, (R, 4)) if timing is not None else None
+        if self.adaptive and tm is None:
             raise TypeError('the gait-adaptive controller needs timing (R,4)')
-        nf = np.broadcast_to(np.asarray(0.0 if nominal_step_frequency is None else nominal_step_frequency, np.float32), (R,))
-        osw = np.broadcast_to(np.asarray(0 if optimize_swing is None else optimize_swing, np.int32), (R,))
-        for r in range(R):
-            self._s_in[r].nominal_step_freq = float(nf[r])
-            self._s_in[r].optimize_swing = int(osw[r])
-        _lib.check(_lib.load().qpmpc_step(h, self._s_in, int(iterations), float(self.cfg.sigma_cem_mppi), self._s_out))
-        o = self._s_out
-        grfs = np.array([o[r].grfs[:] for r in range(R)], np.float32)
-        pred = np.array([o[r].predicted_state[:] for r in range(R)], np.float32)
-        cost = np.array([o[r].best_cost for r in range(R)], np.float32)
-        freq = np.array([o[r].best_freq for r in range(R)], np.float32)
-        idx = np.array([o[r].best_index for r in range(R)], np.int32)
+        nf = None if nominal_step_frequency is None else \
+            np.ascontiguousarray(np.broadcast_to(np.asarray(nominal_step_frequency, np.float32), (R,)))
+        osw = None if optimize_swing is None else \
+            np.ascontiguousarray(np.broadcast_to(np.asarray(optimize_swing, np.int32), (R,)))
+        cem = self.sampling_method == 'cem_mppi'
+        _lib.check(lib.qpmpc_step_flat(
+            h, _fp(st), _fp(rf), _fp(cs), cs.shape[2], _fp(tm), _fp(nf),
+            osw.ctypes.data_as(_IP) if osw is not None else None, int(iterations), float(self.cfg.sigma_cem_mppi),
+            _fp(self._grfs), _fp(self._pred), _fp(self._best), _fp(self._cost), _fp(self._freq),
+            self._idx.ctypes.data_as(_IP), _fp(self._sig) if cem else None))
         self.best_control_parameters = self._best.copy()
         self.master_key = np.array([self.master_key[0], (int(self.master_key[1]) + int(iterations)) & 0xFFFFFFFF], dtype=np.uint32)
-        res = (grfs, pred, self._best.copy(), cost, freq, idx)
-        if self.sampling_method == 'cem_mppi':
+        res = (self._grfs.copy(), self._pred.copy(), self._best.copy(), self._cost.copy(), self._freq.copy(),
+               self._idx.copy())
+        if cem:
             self.sigma_cem_mppi = self._sig.copy()
             res = res + (self._sig.copy(),)
         return res

@@ -740,6 +740,41 @@ extern "C" int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, con
     return QPMPC_OK;
 }
 
+// Structure-of-arrays form of qpmpc_step for R robots kept in flat host arrays (states are RAW, see qpmpc_step).
+extern "C" int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float *references, const float *contacts,
+                               int32_t contact_ld, const float *phase_signals, const float *nominal_step_freqs,
+                               const int32_t *optimize_swing, int32_t iterations, float sigma0, float *grfs,
+                               float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
+                               int32_t *best_indices, float *sigma_new) {
+    if (!h || !states || !references || !contacts) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    const int R = h->R, P = h->P;
+    std::vector<qpmpc_tick_in> in((size_t)R);
+    std::vector<qpmpc_tick_out> out((size_t)R);
+    for (int r = 0; r < R; ++r) {
+        qpmpc_tick_in &i = in[r];
+        memset(&i, 0, sizeof(i));
+        i.state = states + (size_t)r * 24; i.reference = references + (size_t)r * 24;
+        i.contact_sequence = contacts + (size_t)r * 4 * contact_ld; i.contact_ld = contact_ld;
+        i.phase_signal = phase_signals ? phase_signals + (size_t)r * 4 : nullptr;
+        i.nominal_step_freq = nominal_step_freqs ? nominal_step_freqs[r] : 0.f;
+        i.optimize_swing = optimize_swing ? optimize_swing[r] : 0;
+        qpmpc_tick_out &o = out[r];
+        memset(&o, 0, sizeof(o));
+        o.best = best_out ? best_out + (size_t)r * P : nullptr;
+        o.sigma_new = sigma_new ? sigma_new + (size_t)r * P : nullptr;
+    }
+    int rc = qpmpc_step(h, in.data(), iterations, sigma0, out.data());
+    if (rc) return rc;
+    for (int r = 0; r < R; ++r) {
+        if (grfs) memcpy(grfs + (size_t)r * 12, out[r].grfs, 12 * sizeof(float));
+        if (predicted_states) memcpy(predicted_states + (size_t)r * 24, out[r].predicted_state, 24 * sizeof(float));
+        if (best_costs) best_costs[r] = out[r].best_cost;
+        if (best_freqs) best_freqs[r] = out[r].best_freq;
+        if (best_indices) best_indices[r] = out[r].best_index;
+    }
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst) {
     if (!h || !dst || robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "bad argument");
     CK(cudaSetDevice(h->cfg.device));
