@@ -167,6 +167,23 @@ int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float *reference
                     const int32_t *optimize_swing, int32_t iterations, float sigma0, float *grfs,
                     float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
                     int32_t *best_indices, float *sigma_new);
+/* Contact tables from the gait phase clocks, on the device (first half): the horizon look-ahead of
+ * PeriodicGaitGenerator.compute_contact_sequence (helpers/periodic_gait_generator.py:93-118; run() :48-76 per leg, in
+ * float64 like the numpy original) for all R robots.  phase_signal R x 4 (pgg._phase_signal), init R x 4 or NULL
+ * (pgg._init), step_freq R, duty_factor / phase_offset[4] of the gait, (dts, lengths, n_dts) =
+ * contact_sequence_dts / contact_sequence_lenghts.  The R x 4 x H tables stay on the device and are used by the NEXT
+ * qpmpc_tick* / qpmpc_step* call whose inputs pass contact_sequence = NULL (once); `tables` (host, R x 4 x H) receives a
+ * copy unless NULL.  FULL_STANCE gaits need no call: pass tables of ones. */
+int qpmpc_pgg_contact_sequence(qpmpc_handle *h, const double *phase_signal, const uint8_t *init, const double *step_freq,
+                               double duty_factor, const double phase_offset[4], const double *dts,
+                               const int32_t *lengths, int32_t n_dts, float *tables);
+/* Batched epilogue on the device-resident results of the last tick / step (all R robots of the handle):
+ *   grfs_contact[r][3 leg + k] = GRFs * current_contact[leg]                  (srbd_controller_interface.py:225-230)
+ *   tau[r][3 leg + j] = -(J_leg^T grfs_contact_leg)[j]                        (wb_interface.py:372-375)
+ * feet_jac: R x 4 x 3 x 3, leg order FL FR RL RR, J_leg = feet_jac.leg[:, legs_qvel_idx.leg] row-major;
+ * current_contact: R x 4.  Outputs R x 12 each (either may be NULL). */
+int qpmpc_stance_torques(qpmpc_handle *h, const float *feet_jac, const float *current_contact, float *grfs_contact,
+                         float *tau);
 /* costs (N) of the last tick of robot r, fetched lazily (the interface ignores them, I:138,158) */
 int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst);
 

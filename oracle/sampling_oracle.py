@@ -560,3 +560,38 @@ class SamplingOracle:
 def twin64(cfg: OracleConfig) -> SamplingOracle:
     """The float64 twin of an oracle configuration (bounds float32 rounding error in tests)."""
     return SamplingOracle(dataclasses.replace(cfg, dtype=np.float64))
+
+
+# ======================================================================================================================
+# Gait look-ahead of the callers (SURVEY 8f rank 2): helpers/periodic_gait_generator.py (the numpy generator, float64)
+# ======================================================================================================================
+def gait_lookahead_contact_table(phase_signal, init, step_freq, duty_factor, phase_offset, horizon, contact_sequence_dts,
+                                 contact_sequence_lenghts):
+    """`PeriodicGaitGenerator.compute_contact_sequence` (helpers/periodic_gait_generator.py:93-118, non-FULL_STANCE
+    branch) with `run()` (:48-76) restated on copies of the generator's state: phase_signal (4,) float64, init (4,) bool.
+    Returns the (4, horizon) table; the inputs are not modified (the reference restores them, :117)."""
+    t = np.array(phase_signal, dtype=np.float64)
+    ini = [bool(x) for x in (init if init is not None else [False] * 4)]
+    table = np.zeros((len(t), horizon))
+
+    def advance(dt):                                         # run(), :48-76
+        contact = np.zeros(len(t))
+        for leg in range(len(t)):
+            t[leg] += dt * step_freq                         # :53
+            t[leg] = t[leg] % 1.0                            # :56
+            if ini[leg]:                                     # :61-67
+                contact[leg] = 1
+                if not t[leg] <= phase_offset[leg]:
+                    ini[leg] = False
+                    t[leg] = 0
+            else:                                            # :71-74
+                contact[leg] = 1 if t[leg] < duty_factor else 0
+        return contact
+
+    table[:, 0] = advance(0.0)                               # :106
+    j = 0
+    for i in range(1, horizon):                              # :110-115
+        if i >= contact_sequence_lenghts[j]:
+            j += 1
+        table[:, i] = advance(contact_sequence_dts[j])
+    return table

@@ -134,9 +134,12 @@ class BatchedSampling_MPC:
             _lib.check(lib.qpmpc_step_reset(h, key, _fp(_f32(self.best_control_parameters, (R, P))), None))
             self._stateful = True
         st, rf = _f32(states, (R, 24)), _f32(references, (R, 24))
-        cs = _f32(contact_sequences)
-        if cs.ndim != 3 or cs.shape[0] != R or cs.shape[1] != 4 or cs.shape[2] < H:
-            raise _lib.QpmpcError(_lib.ERR_INVALID, f'contact_sequences must be ({R}, 4, >= {H}), got {cs.shape}')
+        cs, ld = None, H                   # None: the tables made by gait.contact_sequences_from_phase are on the device
+        if contact_sequences is not None:
+            cs = _f32(contact_sequences)
+            if cs.ndim != 3 or cs.shape[0] != R or cs.shape[1] != 4 or cs.shape[2] < H:
+                raise _lib.QpmpcError(_lib.ERR_INVALID, f'contact_sequences must be ({R}, 4, >= {H}), got {cs.shape}')
+            ld = cs.shape[2]
         tm = _f32(timing, (R, 4)) if timing is not None else None
         if self.adaptive and tm is None:
             raise TypeError('the gait-adaptive controller needs timing (R,4)')
@@ -146,7 +149,7 @@ class BatchedSampling_MPC:
             np.ascontiguousarray(np.broadcast_to(np.asarray(optimize_swing, np.int32), (R,)))
         cem = self.sampling_method == 'cem_mppi'
         _lib.check(lib.qpmpc_step_flat(
-            h, _fp(st), _fp(rf), _fp(cs), cs.shape[2], _fp(tm), _fp(nf),
+            h, _fp(st), _fp(rf), _fp(cs), ld, _fp(tm), _fp(nf),
             osw.ctypes.data_as(_IP) if osw is not None else None, int(iterations), float(self.cfg.sigma_cem_mppi),
             _fp(self._grfs), _fp(self._pred), _fp(self._best), _fp(self._cost), _fp(self._freq),
             self._idx.ctypes.data_as(_IP), _fp(self._sig) if cem else None))
@@ -158,6 +161,16 @@ class BatchedSampling_MPC:
             self.sigma_cem_mppi = self._sig.copy()
             res = res + (self._sig.copy(),)
         return res
+
+    def stance_torques(self, feet_jac, current_contact):
+        """Batched epilogue on the device-resident GRFs of the last tick:
+        nmpc_GRFs * current_contact (I:225-230) and tau = -J^T nmpc_GRFs per leg (wb_interface.py:372-375).
+        feet_jac (R,4,3,3) = feet_jac.leg[:, legs_qvel_idx.leg]; current_contact (R,4) -> (grfs (R,12), tau (R,12))."""
+        R = self.num_robots
+        jac, con = _f32(feet_jac, (R, 4, 3, 3)), _f32(current_contact, (R, 4))
+        grf, tau = np.empty((R, 12), np.float32), np.empty((R, 12), np.float32)
+        _lib.check(_lib.load().qpmpc_stance_torques(self._ensure(), _fp(jac), _fp(con), _fp(grf), _fp(tau)))
+        return grf, tau
 
     def generate_noise(self, robot: int, key=None, sigma=None) -> np.ndarray:
         """additional_random_parameters (N,P) robot `robot` of this batch draws for `key` (parity / debugging)."""

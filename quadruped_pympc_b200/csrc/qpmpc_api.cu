@@ -61,6 +61,53 @@ __global__ void freq_export_kernel(const __grid_constant__ KParams kp, const flo
         dst[i] = sample_step_freq<METHOD>(kp, in_rec, kp.seed, kp.robot_base, 0, i);
 }
 
+// Batched epilogue of the tick: what the callers do next with the GRFs of every robot --
+//   nmpc_GRFs.leg = GRFs[3 leg : 3 leg + 3] * current_contact[leg]            (srbd_controller_interface.py:225-230)
+//   tau.leg = -J_leg^T nmpc_GRFs.leg,  J_leg = feet_jac.leg[:, legs_qvel_idx.leg] (3 x 3)   (wb_interface.py:372-375)
+// read straight from the device-resident result packets of the last tick.  One thread per (robot, leg, joint).
+__global__ void stance_torque_kernel(const float *out_packets, int out_stride, const float *jac, const float *contact,
+                                     float *grf_masked, float *tau, int R) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R * 12) return;
+    const int r = i / 12, lj = i - r * 12, leg = lj / 3, j = lj - leg * 3;
+    const float c = contact[r * 4 + leg];
+    const float *F = out_packets + (size_t)r * out_stride + OUT_GRF + 3 * leg;
+    const float *J = jac + (size_t)r * 36 + leg * 9;                 // row-major 3 x 3: J[k][j] = d foot_k / d q_j
+    const float f0 = F[0] * c, f1 = F[1] * c, f2 = F[2] * c;
+    grf_masked[i] = (j == 0 ? f0 : (j == 1 ? f1 : f2));
+    tau[i] = -((J[0 * 3 + j] * f0 + J[1 * 3 + j] * f1) + J[2 * 3 + j] * f2);
+}
+
+// Contact tables of R robots from their gait phase clocks (first half): the horizon look-ahead of the
+// reference's PeriodicGaitGenerator.compute_contact_sequence (helpers/periodic_gait_generator.py:93-118) with run()
+// (:48-76) unrolled per leg, in float64 like the numpy original (the phase comparisons are discontinuities).
+// One thread per (robot, leg).  table: [R][4][H] float 0/1.
+struct PggParams {
+    double duty, offset[4], dts[QPMPC_MAX_HORIZON];
+    int H, R;
+};
+__global__ void pgg_contact_kernel(const __grid_constant__ PggParams pp, const double *phase, const unsigned char *init,
+                                   const double *step_freq, float *table) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pp.R * 4) return;
+    const int r = i >> 2, leg = i & 3;
+    double t = phase[i];
+    bool in_init = init ? (init[i] != 0) : false;
+    const double f = step_freq[r];
+    for (int n = 0; n < pp.H; ++n) {
+        t = __dadd_rn(t, __dmul_rn(pp.dts[n], f));        // self._phase_signal[leg] += dt * new_step_freq   (:53)
+        t = t - floor(t);                                  // % 1.0 (exact for t >= 0)                        (:56)
+        float c;
+        if (in_init) {                                     // :61-67
+            if (t <= pp.offset[leg]) c = 1.0f;
+            else { in_init = false; c = 1.0f; t = 0.0; }
+        } else {
+            c = (t < pp.duty) ? 1.0f : 0.0f;               // :71-74
+        }
+        table[((size_t)r * 4 + leg) * pp.H + n] = c;
+    }
+}
+
 __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
     float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
 #pragma unroll 1
@@ -150,6 +197,10 @@ struct qpmpc_handle {
     // peer exchange (fused collective of a sample-sharded controller, qpmpc_tick.cuh peer_exchange)
     float *d_mbox = nullptr;          // this rank's mailbox (cudaMalloc: exportable with cudaIpcGetMemHandle)
     float *d_sink = nullptr;
+    float *d_contact = nullptr;       // [R][4][H] contact tables generated on the device (qpmpc_pgg_contact_sequence)
+    void *d_pgg = nullptr;            // its inputs: R x 4 phases (f64), R step frequencies (f64), R x 4 init flags
+    bool contacts_on_device = false;  // armed by qpmpc_pgg_contact_sequence, consumed by the next tick / step
+    float *d_epi = nullptr;           // stance-torque epilogue scratch: [R][36 jac + 4 contact + 12 grf + 12 tau]
     float *d_ctrl = nullptr;          // stateful controller records (qpmpc_step): [R][ctrl_stride]
     int ctrl_stride = 0;          // loopback test hook: where the records pushed to absent peers go
     float *peer_mbox[MAX_PEERS] = {}; // every rank's mailbox as seen from this device
@@ -231,7 +282,7 @@ static void free_handle(qpmpc_handle *h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
-    cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl);
+    cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -412,8 +463,9 @@ static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explicit_params, bool stateful = false) {
     const KParams &kp = h->kp;
     float *rec = h->h_in + (size_t)r * kp.in_stride;
-    if (!in->state || !in->reference || !in->contact_sequence) return fail(QPMPC_ERR_INVALID, "state / reference / contact_sequence must not be NULL");
-    if (in->contact_ld < h->H) return fail(QPMPC_ERR_INVALID, "contact_ld %d < horizon %d", in->contact_ld, h->H);
+    if (!in->state || !in->reference) return fail(QPMPC_ERR_INVALID, "state / reference must not be NULL");
+    if (!in->contact_sequence && !h->contacts_on_device) return fail(QPMPC_ERR_INVALID, "contact_sequence is NULL and no device-generated table is armed (qpmpc_pgg_contact_sequence)");
+    if (in->contact_sequence && in->contact_ld < h->H) return fail(QPMPC_ERR_INVALID, "contact_ld %d < horizon %d", in->contact_ld, h->H);
     memcpy(rec + IN_STATE, in->state, 24 * sizeof(float));
     memcpy(rec + IN_REF, in->reference, 24 * sizeof(float));
     for (int l = 0; l < 4; ++l) rec[IN_PHASE + l] = in->phase_signal ? in->phase_signal[l] : 0.f;
@@ -426,7 +478,7 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     rec[IN_SEED] = u2f(in->key[0]);
     rec[IN_TICK] = u2f(in->key[1]);
     rec[IN_ROBOT] = u2f((uint32_t)(h->cfg.robot_base + r));   // global robot id = Philox key word 1
-    for (int l = 0; l < 4; ++l)
+    for (int l = 0; l < 4 && in->contact_sequence; ++l)
         for (int n = 0; n < h->H; ++n) {
             const float c = in->contact_sequence[(size_t)l * in->contact_ld + n];
             if (c != 0.0f && c != 1.0f) return fail(QPMPC_ERR_INVALID, "contact_sequence[%d][%d] = %g is not 0 or 1", l, n, (double)c);
@@ -532,6 +584,49 @@ static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *
     return QPMPC_OK;
 }
 
+// Device-generated contact tables (qpmpc_pgg_contact_sequence) are used by the next tick / step whose inputs carry no
+// host table, once.
+static void bind_device_contacts(qpmpc_handle *h, const qpmpc_tick_in *in, KParams &kp) {
+    if (h->contacts_on_device && in[0].contact_sequence == nullptr) kp.contact_dev = h->d_contact;
+    h->contacts_on_device = false;
+}
+
+extern "C" int qpmpc_pgg_contact_sequence(qpmpc_handle *h, const double *phase_signal, const uint8_t *init,
+                                          const double *step_freq, double duty_factor, const double phase_offset[4],
+                                          const double *dts, const int32_t *lengths, int32_t n_dts, float *tables) {
+    if (!h || !phase_signal || !step_freq || !phase_offset || !dts || !lengths || n_dts < 1) return fail(QPMPC_ERR_INVALID, "NULL / bad argument");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t R = h->R;
+    const int H = h->H;
+    PggParams pp;
+    memset(&pp, 0, sizeof(pp));
+    pp.duty = duty_factor; pp.H = H; pp.R = (int)R;
+    memcpy(pp.offset, phase_offset, 4 * sizeof(double));
+    pp.dts[0] = 0.0;                                       // contact_sequence[:, 0] = self.run(0.0, self.step_freq)   (:106)
+    for (int i = 1, j = 0; i < H; ++i) {                   // :110-115
+        if (i >= lengths[j]) { if (j + 1 >= n_dts) return fail(QPMPC_ERR_INVALID, "contact_sequence_lenghts do not cover the horizon"); ++j; }
+        pp.dts[i] = dts[j];
+    }
+    const size_t in_bytes = R * 4 * sizeof(double) + R * sizeof(double) + R * 4;
+    if (!h->d_pgg) CK(cudaMalloc(&h->d_pgg, in_bytes));
+    if (!h->d_contact) CK(cudaMalloc((void **)&h->d_contact, R * 4 * H * sizeof(float)));
+    double *d_phase = (double *)h->d_pgg, *d_freq = d_phase + R * 4;
+    unsigned char *d_init = (unsigned char *)(d_freq + R);
+    CK(cudaMemcpyAsync(d_phase, phase_signal, R * 4 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_freq, step_freq, R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (init) CK(cudaMemcpyAsync(d_init, init, R * 4, cudaMemcpyHostToDevice, h->stream));
+    const int threads = 128, blocks = (int)((R * 4 + threads - 1) / threads);
+    pgg_contact_kernel<<<blocks, threads, 0, h->stream>>>(pp, d_phase, init ? d_init : nullptr, d_freq, h->d_contact);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (tables) {
+        CK(cudaMemcpyAsync(tables, h->d_contact, R * 4 * H * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    h->contacts_on_device = true;                          // the tick kernels of this stream run after the table kernel
+    return QPMPC_OK;
+}
+
 static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
     if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
     if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: use qpmpc_tick_sharded / qpmpc_shard_partial");
@@ -539,6 +634,7 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
     const int R = h->R;
     for (int r = 0; r < R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
     KParams kp = h->kp;
+    bind_device_contacts(h, in, kp);
     int rc = stage_injection(h, in, R, kp);
     if (rc) return rc;
     const bool plain = (kp.noise_mode == NOISE_PHILOX && !kp.freq_injected);
@@ -546,7 +642,7 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
     const dim3 grid(kp.nblk, R);
     const bool mapped = h->cfg.io_mode == QPMPC_IO_MAPPED;
     if (plain && h->direct) return direct_tick(h, kp, grid, out);
-    if (plain && h->cfg.use_graph && !mapped) {
+    if (plain && h->cfg.use_graph && !mapped && kp.contact_dev == nullptr) {   // (the graph is captured without device tables)
         if (!h->graph_exec) {                      // capture (H2D, kernel, D2H) once; the packet addresses never change
             cudaGraph_t g = nullptr;
             CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
@@ -588,6 +684,7 @@ extern "C" int qpmpc_tick_iterations(qpmpc_handle *h, const qpmpc_tick_in *in, i
         if (rc) return rc;
     }
     KParams kp = h->kp;
+    bind_device_contacts(h, in, kp);
     kp.in = h->d_in; kp.out = h->d_out;                      // the carried state lives in the device copy of the packet
     kp.carry_best = 1;
     CK(cudaMemcpyAsync(h->d_in, h->h_in, (size_t)R * kp.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream));
@@ -673,6 +770,7 @@ extern "C" int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iter
     }
     h->kp.seed = seed;                                 // pack_one took key[0] of the (ignored) input keys
     KParams kp = h->kp;
+    bind_device_contacts(h, in, kp);
     kp.ctrl_state = h->d_ctrl; kp.ctrl_stride = h->ctrl_stride; kp.sigma0 = sigma0;
     const dim3 grid(kp.nblk, R);
     const bool direct = h->direct;
@@ -708,7 +806,7 @@ extern "C" int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, con
                                        const float *nominal_step_freqs, const int32_t *optimize_swing, const uint32_t key[2],
                                        float *grfs, float *predicted_states, float *best_out, float *best_costs,
                                        float *best_freqs, int32_t *best_indices, float *sigma_new) {
-    if (!h || !states || !references || !contacts || !key) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h || !states || !references || !key) return fail(QPMPC_ERR_INVALID, "NULL argument");
     const int R = h->R, P = h->P;
     std::vector<qpmpc_tick_in> in((size_t)R);
     std::vector<qpmpc_tick_out> out((size_t)R);
@@ -716,7 +814,7 @@ extern "C" int qpmpc_tick_batched_flat(qpmpc_handle *h, const float *states, con
         qpmpc_tick_in &i = in[r];
         memset(&i, 0, sizeof(i));
         i.state = states + (size_t)r * 24; i.reference = references + (size_t)r * 24;
-        i.contact_sequence = contacts + (size_t)r * 4 * contact_ld; i.contact_ld = contact_ld;
+        i.contact_sequence = contacts ? contacts + (size_t)r * 4 * contact_ld : nullptr; i.contact_ld = contact_ld;
         i.best = best ? best + (size_t)r * P : nullptr;
         i.sigma = sigma ? sigma + (size_t)r * P : nullptr;
         i.phase_signal = phase_signals ? phase_signals + (size_t)r * 4 : nullptr;
@@ -746,7 +844,7 @@ extern "C" int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float
                                const int32_t *optimize_swing, int32_t iterations, float sigma0, float *grfs,
                                float *predicted_states, float *best_out, float *best_costs, float *best_freqs,
                                int32_t *best_indices, float *sigma_new) {
-    if (!h || !states || !references || !contacts) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (!h || !states || !references) return fail(QPMPC_ERR_INVALID, "NULL argument");
     const int R = h->R, P = h->P;
     std::vector<qpmpc_tick_in> in((size_t)R);
     std::vector<qpmpc_tick_out> out((size_t)R);
@@ -754,7 +852,7 @@ extern "C" int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float
         qpmpc_tick_in &i = in[r];
         memset(&i, 0, sizeof(i));
         i.state = states + (size_t)r * 24; i.reference = references + (size_t)r * 24;
-        i.contact_sequence = contacts + (size_t)r * 4 * contact_ld; i.contact_ld = contact_ld;
+        i.contact_sequence = contacts ? contacts + (size_t)r * 4 * contact_ld : nullptr; i.contact_ld = contact_ld;
         i.phase_signal = phase_signals ? phase_signals + (size_t)r * 4 : nullptr;
         i.nominal_step_freq = nominal_step_freqs ? nominal_step_freqs[r] : 0.f;
         i.optimize_swing = optimize_swing ? optimize_swing[r] : 0;
@@ -772,6 +870,25 @@ extern "C" int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float
         if (best_freqs) best_freqs[r] = out[r].best_freq;
         if (best_indices) best_indices[r] = out[r].best_index;
     }
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_stance_torques(qpmpc_handle *h, const float *feet_jac, const float *current_contact,
+                                    float *grfs_contact, float *tau) {
+    if (!h || !feet_jac || !current_contact) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t R = h->R;
+    if (!h->d_epi) CK(cudaMalloc((void **)&h->d_epi, R * 64 * sizeof(float)));
+    float *d_jac = h->d_epi, *d_con = d_jac + R * 36, *d_grf = d_con + R * 4, *d_tau = d_grf + R * 12;
+    CK(cudaMemcpyAsync(d_jac, feet_jac, R * 36 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_con, current_contact, R * 4 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    const int threads = 128, blocks = (int)((R * 12 + threads - 1) / threads);
+    stance_torque_kernel<<<blocks, threads, 0, h->stream>>>(h->kout, h->kp.out_stride, d_jac, d_con, d_grf, d_tau, (int)R);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (grfs_contact) CK(cudaMemcpyAsync(grfs_contact, d_grf, R * 12 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (tau) CK(cudaMemcpyAsync(tau, d_tau, R * 12 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     return QPMPC_OK;
 }
 

@@ -85,6 +85,7 @@ struct KParams {
     // ---- peer exchange of a sample-sharded controller (fused collective, qpmpc_tick.cuh peer_exchange) ----
     // ---- stateful controller (qpmpc_step): best / sigma / Philox tick / previous contact live on the
     //      device across ticks; the host uploads only state, reference, phase, frequency and the contact table ----
+    const float *contact_dev;               // [R][4][H] contact tables made on the device (qpmpc_pgg_contact_sequence), or NULL
     float *ctrl_state;                      // [R][ctrl_stride] = {best P, sigma P, tick u32, prev-contact mask u32, pad}, or NULL
     int ctrl_stride;
     int sigma_reset;                        // 1: this launch starts from sigma0 (I:128-129: reset at iteration 0 of every tick)

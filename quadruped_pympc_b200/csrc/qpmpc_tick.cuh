@@ -39,13 +39,18 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
     const float *gin = kp.param_packet ? kp.packet : kp.in + (size_t)r * kp.in_stride;
     if (kp.ctrl_state == nullptr) {
         for (int k = threadIdx.x; k < kp.in_stride; k += TB) s.in[k] = gin[k];
+        if (kp.contact_dev) {                                     // tables generated on the device replace the packet's
+            __syncthreads();
+            for (int k = threadIdx.x; k < 4 * kp.H; k += TB) s.in[IN_CONTACT + k] = __ldcg(kp.contact_dev + (size_t)r * 4 * kp.H + k);
+        }
         __syncthreads();
     } else {
         // Stateful controller: the packet carries what the host knows this tick (raw state, reference, phase, frequency,
         // contact table); best, sigma, the Philox tick and the previous contact come from the device-resident record.
         // Then the host prep of the reference, S:563-627 (prepare_state_and_reference), on the shared-memory copy:
         const float *st = kp.ctrl_state + (size_t)r * kp.ctrl_stride;
-        for (int k = threadIdx.x; k < kp.off_best; k += TB) s.in[k] = gin[k];
+        for (int k = threadIdx.x; k < kp.off_best; k += TB)
+            s.in[k] = (kp.contact_dev && k >= IN_CONTACT) ? __ldcg(kp.contact_dev + (size_t)r * 4 * kp.H + (k - IN_CONTACT)) : gin[k];
         for (int k = threadIdx.x; k < 2 * kp.P; k += TB) {
             float v = __ldcg(st + k);
             if (kp.sigma_reset && k >= kp.P) v = kp.sigma0;

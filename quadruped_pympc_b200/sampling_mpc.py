@@ -502,6 +502,15 @@ class Sampling_MPC:
         _lib.check(_lib.load().qpmpc_step_state(h, 0, _fp(best), _fp(sigma), pc, key))
         return best, sigma, np.array(pc[:]), np.array(key[:], np.uint32)
 
+    def stance_torques(self, feet_jac, current_contact):
+        """Epilogue on the device-resident GRFs of the last tick: nmpc_GRFs * current_contact
+        (I:225-230) and tau = -J^T nmpc_GRFs per leg (wb_interface.py:372-375).  feet_jac (4,3,3) =
+        feet_jac.leg[:, legs_qvel_idx.leg]; current_contact (4,) -> (grfs (12,), tau (12,))."""
+        jac, con = _f32(feet_jac, (4, 3, 3)), _f32(current_contact, (4,))
+        grf, tau = np.empty(12, np.float32), np.empty(12, np.float32)
+        _lib.check(_lib.load().qpmpc_stance_torques(self._ensure(), _fp(jac), _fp(con), _fp(grf), _fp(tau)))
+        return grf, tau
+
     def _tick(self, state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing, noise,
               step_freqs, iterations=1):
         h = self._ensure()

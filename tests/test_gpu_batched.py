@@ -152,3 +152,33 @@ def test_stateful_batch_step_equals_per_robot_host_loops(built, method, iters):
                 np.testing.assert_array_equal(out_d[k][r], o[k][0])
             if cem:
                 np.testing.assert_array_equal(out_d[6][r], o[6][0])
+
+
+def test_stance_torque_epilogue(built):
+    """GRFs * current_contact (I:225-230) and tau = -J^T GRF per leg (wb_interface.py:372-375) on the
+    device-resident results, against the reference's numpy expressions in float64."""
+    R, N = 6, 600
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=N)
+    b = BatchedSampling_MPC(cfg, R)
+    st, rf, cs, ph, _ = _scenarios('go2', R)
+    out = b.with_newkey().compute_control(st, rf, cs)
+    rng = np.random.RandomState(4)
+    jac = rng.randn(R, 4, 3, 3).astype(np.float32)             # feet_jac.leg[:, legs_qvel_idx.leg]
+    contact = cs[:, :, 0]
+    grf, tau = b.stance_torques(jac, contact)
+    for r in range(R):
+        for leg in range(4):
+            F = out[0][r, 3 * leg:3 * leg + 3].astype(np.float64) * float(contact[r, leg])
+            want = -np.matmul(jac[r, leg].astype(np.float64).T, F)
+            np.testing.assert_allclose(grf[r, 3 * leg:3 * leg + 3], F, rtol=1e-7, atol=0)
+            np.testing.assert_allclose(tau[r, 3 * leg:3 * leg + 3], want, rtol=1e-5, atol=1e-4)
+    # single controller, direct I/O: the result packet is device-resident as well
+    c = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario('go2', 'trot', seed=0)
+    o = c.with_newkey().jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], np.zeros(96, np.float32),
+                                               c.master_key, sc['phase_signal'], 1.4, 0)
+    g1, t1 = c.stance_torques(jac[0], sc['contact_sequence'][:, 0])
+    for leg in range(4):
+        F = o[0][3 * leg:3 * leg + 3].astype(np.float64) * float(sc['contact_sequence'][leg, 0])
+        np.testing.assert_allclose(t1[3 * leg:3 * leg + 3], -np.matmul(jac[0, leg].astype(np.float64).T, F), rtol=1e-5, atol=1e-4)
+        np.testing.assert_allclose(g1[3 * leg:3 * leg + 3], F, rtol=1e-7)
