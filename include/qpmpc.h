@@ -177,6 +177,19 @@ int qpmpc_step_flat(qpmpc_handle *h, const float *states, const float *reference
 int qpmpc_pgg_contact_sequence(qpmpc_handle *h, const double *phase_signal, const uint8_t *init, const double *step_freq,
                                double duty_factor, const double phase_offset[4], const double *dts,
                                const int32_t *lengths, int32_t n_dts, float *tables);
+/* Reference footholds of the R robots, on the device (second half): FootholdReferenceGenerator.
+ * compute_footholds_reference (helpers/foothold_reference_generator.py:53-157; call site interfaces/wb_interface.py:
+ * 231-238) in float64: base_position R x 3, base_ori_euler_xyz R x 3, base_xy_lin_vel / ref_base_xy_lin_vel R x 2 (world
+ * frame), hips_position R x 4 x 3 (FL FR RL RR), lift_off_z R x 4 (frg.lift_off_positions[leg][2]), stance_time R
+ * (frg.stance_time); com_height_nominal = simulation_params['ref_z'], hip_height / hip_offset (0.1, :44) / gravity
+ * (config.gravity_constant) of the generator, com_pos_offset_b (3) or NULL = zeros.  The generator's state -- the deque
+ * of the last 20 horizontal-frame base velocities (:16,27,98-99) -- is kept per robot on the device; reset_history != 0
+ * empties it before this call (= a freshly constructed generator).  ref_feet: R x 4 x 3 (host), world frame. */
+int qpmpc_footholds_reference(qpmpc_handle *h, const double *base_position, const double *base_ori_euler_xyz,
+                              const double *base_xy_lin_vel, const double *ref_base_xy_lin_vel,
+                              const double *hips_position, const double *lift_off_z, const double *stance_time,
+                              double com_height_nominal, double hip_height, double hip_offset, double gravity,
+                              const double *com_pos_offset_b, int32_t reset_history, double *ref_feet);
 /* Batched epilogue on the device-resident results of the last tick / step (all R robots of the handle):
  *   grfs_contact[r][3 leg + k] = GRFs * current_contact[leg]                  (srbd_controller_interface.py:225-230)
  *   tau[r][3 leg + j] = -(J_leg^T grfs_contact_leg)[j]                        (wb_interface.py:372-375)

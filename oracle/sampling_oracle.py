@@ -595,3 +595,49 @@ def gait_lookahead_contact_table(phase_signal, init, step_freq, duty_factor, pha
             j += 1
         table[:, i] = advance(contact_sequence_dts[j])
     return table
+
+
+class FootholdReferenceOracle:
+    """TEST INFRASTRUCTURE.  numpy float64 restatement of FootholdReferenceGenerator.compute_footholds_reference
+    (helpers/foothold_reference_generator.py:53-157) for one robot; state = the deque of the last
+    `vel_moving_average_length` horizontal-frame base velocities (:16,27).  Pinned against the reference class itself by
+    tests/golden/gait_footholds.npz (tools/make_golden_footholds.py)."""
+
+    def __init__(self, stance_time, lift_off_z, hip_height, hip_offset=0.1, gravity=9.81, vel_moving_average_length=20):
+        self.stance_time, self.hip_height, self.hip_offset, self.gravity = stance_time, hip_height, hip_offset, gravity
+        self.lift_off_z = np.asarray(lift_off_z, np.float64).copy()      # (4,) FL FR RL RR
+        self.length = vel_moving_average_length
+        self.hist = []
+        self.com_pos_offset_b = np.zeros(3)                              # :32
+
+    def __call__(self, base_position, base_ori_euler_xyz, base_xy_lin_vel, ref_base_xy_lin_vel, hips_position,
+                 com_height_nominal):
+        base_position, hips = np.asarray(base_position, np.float64), np.asarray(hips_position, np.float64).reshape(4, 3)
+        roll, pitch, yaw = (float(a) for a in base_ori_euler_xyz)
+        c, s = np.cos(yaw), np.sin(yaw)
+        w2h = np.array([[c, s], [-s, c]])                                # :87-90
+        v_h = w2h @ np.asarray(base_xy_lin_vel, np.float64)              # :93
+        rv_h = w2h @ np.asarray(ref_base_xy_lin_vel, np.float64)         # :94
+        self.hist.append(v_h)                                            # deque(maxlen), :97
+        self.hist = self.hist[-self.length:]
+        acc = np.zeros(2)
+        for v in self.hist:                                              # np.mean(axis=0): row after row, :98
+            acc = acc + v
+        mvg = acc / len(self.hist)
+        lim = self.hip_height * 1.5
+        delta = np.minimum(np.maximum((self.stance_time / 2.0) * rv_h, -lim), lim)          # :104-105
+        err = np.sqrt(com_height_nominal / self.gravity) * (mvg - rv_h)                     # :109
+        err = np.minimum(np.maximum(err, -0.05), 0.05)                                      # :110-111
+        cr, sr, cp, sp = np.cos(roll), np.sin(roll), np.cos(pitch), np.sin(pitch)
+        b2w = np.array([[c * cp, c * sp * sr - s * cr, c * sp * cr + s * sr],               # extrinsic xyz = Rz Ry Rx, :140
+                        [s * cp, s * sp * sr + c * cr, s * sp * cr - c * sr],
+                        [-sp, cp * sr, cp * cr]])
+        off_w = b2w @ self.com_pos_offset_b                                                 # :141
+        out = np.zeros((4, 3))
+        for leg in range(4):
+            f = w2h @ (hips[leg, :2] - base_position[:2])                                   # :118-121
+            f[1] += self.hip_offset if leg in (0, 2) else -self.hip_offset                  # :126-129
+            f = f + (delta + err)                                                           # :131
+            out[leg, :2] = w2h.T @ f + base_position[:2] + off_w[:2]                        # :134-146
+            out[leg, 2] = self.lift_off_z[leg]                                              # :150-151
+        return out

@@ -108,6 +108,71 @@ __global__ void pgg_contact_kernel(const __grid_constant__ PggParams pp, const d
     }
 }
 
+// Reference footholds of R robots (second half): FootholdReferenceGenerator.
+// compute_footholds_reference (helpers/foothold_reference_generator.py:53-157) -- hip-centric heuristic with the desired-
+// velocity offset, the moving-average velocity-error compensation and the manual CoM offset -- in float64 like the numpy
+// original, one thread per robot (the per-leg work is 4 x a 2 x 2 rotation).  The generator's only state, the deque of
+// the last 20 horizontal-frame base velocities (:27,98-99), lives in a device ring per robot.
+constexpr int FRG_HIST = 20;                                 // vel_moving_average_length, :16
+struct FrgParams {
+    double com_height_nominal, hip_height, hip_offset, gravity, com_off_b[3];
+    int R;
+};
+// hist: [R][FRG_HIST][2] ring, meta: [R][2] = {count, next slot}; feet out: [R][4][3]
+__global__ void foothold_reference_kernel(const __grid_constant__ FrgParams fp, const double *base_pos, const double *euler,
+                                          const double *vel_xy, const double *ref_vel_xy, const double *hips,
+                                          const double *lift_off_z, const double *stance_time, double *hist, int *meta,
+                                          double *feet) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= fp.R) return;
+    const double yaw = euler[3 * r + 2];
+    const double cy = cos(yaw), sy = sin(yaw);               // R_W2H = [[cy, sy], [-sy, cy]], :88-90
+    const double vx = vel_xy[2 * r], vy = vel_xy[2 * r + 1], rvx = ref_vel_xy[2 * r], rvy = ref_vel_xy[2 * r + 1];
+    const double vHx = __dadd_rn(__dmul_rn(cy, vx), __dmul_rn(sy, vy)), vHy = __dadd_rn(__dmul_rn(-sy, vx), __dmul_rn(cy, vy));     // :93
+    const double rHx = __dadd_rn(__dmul_rn(cy, rvx), __dmul_rn(sy, rvy)), rHy = __dadd_rn(__dmul_rn(-sy, rvx), __dmul_rn(cy, rvy)); // :94
+    // moving average over the deque (append, then mean oldest -> newest), :97-99
+    double *hr = hist + (size_t)r * FRG_HIST * 2;
+    int count = meta[2 * r], next = meta[2 * r + 1];
+    hr[2 * next] = vHx; hr[2 * next + 1] = vHy;
+    next = (next + 1) % FRG_HIST;
+    if (count < FRG_HIST) ++count;
+    meta[2 * r] = count; meta[2 * r + 1] = next;
+    double sx = 0.0, sy2 = 0.0;
+    const int oldest = (next - count + FRG_HIST) % FRG_HIST;
+    for (int k = 0; k < count; ++k) { const int j = (oldest + k) % FRG_HIST; sx = __dadd_rn(sx, hr[2 * j]); sy2 = __dadd_rn(sy2, hr[2 * j + 1]); }
+    const double mx = sx / (double)count, my = sy2 / (double)count;
+    // desired-velocity offset, clipped to +-1.5 hip heights, :104-106
+    const double half_stance = stance_time[r] / 2.0, lim = __dmul_rn(fp.hip_height, 1.5);
+    double dx = __dmul_rn(half_stance, rHx), dy = __dmul_rn(half_stance, rHy);
+    dx = fmin(fmax(dx, -lim), lim); dy = fmin(fmax(dy, -lim), lim);
+    // velocity-error compensation, clipped to +-0.05, :109-112
+    const double kk = sqrt(fp.com_height_nominal / fp.gravity);
+    double ex = __dmul_rn(kk, __dadd_rn(mx, -rHx)), ey = __dmul_rn(kk, __dadd_rn(my, -rHy));
+    ex = ex > 0.05 ? 0.05 : ex; ex = ex < -0.05 ? -0.05 : ex;
+    ey = ey > 0.05 ? 0.05 : ey; ey = ey < -0.05 ? -0.05 : ey;
+    const double ox = __dadd_rn(dx, ex), oy = __dadd_rn(dy, ey);         // vel_offset + error_compensation, :131
+    // manual CoM offset in world frame: R_B2W = Rotation.from_euler("xyz", euler) = Rz Ry Rx, :140-142
+    const double roll = euler[3 * r], pitch = euler[3 * r + 1];
+    const double cr = cos(roll), sr = sin(roll), cp = cos(pitch), sp = sin(pitch);
+    const double bx = fp.com_off_b[0], by = fp.com_off_b[1], bz = fp.com_off_b[2];
+    const double cwx = (cy * cp) * bx + (cy * sp * sr - sy * cr) * by + (cy * sp * cr + sy * sr) * bz;
+    const double cwy = (sy * cp) * bx + (sy * sp * sr + cy * cr) * by + (sy * sp * cr - cy * sr) * bz;
+    const double px = base_pos[3 * r], py = base_pos[3 * r + 1];
+    for (int leg = 0; leg < 4; ++leg) {
+        const double hx = __dadd_rn(hips[(r * 4 + leg) * 3], -px), hy = __dadd_rn(hips[(r * 4 + leg) * 3 + 1], -py);
+        double fx = __dadd_rn(__dmul_rn(cy, hx), __dmul_rn(sy, hy));      // R_W2H @ (hip - base), :118-121
+        double fy = __dadd_rn(__dmul_rn(-sy, hx), __dmul_rn(cy, hy));
+        fy = (leg == 0 || leg == 2) ? __dadd_rn(fy, fp.hip_offset) : __dadd_rn(fy, -fp.hip_offset);   // :126-129
+        fx = __dadd_rn(fx, ox); fy = __dadd_rn(fy, oy);                   // :131
+        double wx = __dadd_rn(__dadd_rn(__dmul_rn(cy, fx), __dmul_rn(-sy, fy)), px);   // R_W2H.T @ f + base, :134-137
+        double wy = __dadd_rn(__dadd_rn(__dmul_rn(sy, fx), __dmul_rn(cy, fy)), py);
+        wx = __dadd_rn(wx, cwx); wy = __dadd_rn(wy, cwy);                 // :143-146
+        const double wz = lift_off_z[r * 4 + leg];                        // :150-151
+        double *o = feet + ((size_t)r * 4 + leg) * 3;
+        o[0] = wx; o[1] = wy; o[2] = wz;
+    }
+}
+
 __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
     float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
 #pragma unroll 1
@@ -200,6 +265,7 @@ struct qpmpc_handle {
     float *d_contact = nullptr;       // [R][4][H] contact tables generated on the device (qpmpc_pgg_contact_sequence)
     void *d_pgg = nullptr;            // its inputs: R x 4 phases (f64), R step frequencies (f64), R x 4 init flags
     bool contacts_on_device = false;  // armed by qpmpc_pgg_contact_sequence, consumed by the next tick / step
+    void *d_frg = nullptr;            // foothold reference: inputs, velocity-history rings, outputs (qpmpc_footholds_reference)
     float *d_epi = nullptr;           // stance-torque epilogue scratch: [R][36 jac + 4 contact + 12 grf + 12 tau]
     float *d_ctrl = nullptr;          // stateful controller records (qpmpc_step): [R][ctrl_stride]
     int ctrl_stride = 0;          // loopback test hook: where the records pushed to absent peers go
@@ -282,7 +348,7 @@ static void free_handle(qpmpc_handle *h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
-    cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg);
+    cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg); cudaFree(h->d_frg);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -624,6 +690,51 @@ extern "C" int qpmpc_pgg_contact_sequence(qpmpc_handle *h, const double *phase_s
         CK(cudaStreamSynchronize(h->stream));
     }
     h->contacts_on_device = true;                          // the tick kernels of this stream run after the table kernel
+    return QPMPC_OK;
+}
+
+// layout of d_frg (doubles): base_pos 3R | euler 3R | vel 2R | ref vel 2R | hips 12R | lift_off_z 4R | stance R | feet 12R |
+// hist 40R | then (ints) meta 2R
+extern "C" int qpmpc_footholds_reference(qpmpc_handle *h, const double *base_position, const double *base_ori_euler_xyz,
+                                         const double *base_xy_lin_vel, const double *ref_base_xy_lin_vel,
+                                         const double *hips_position, const double *lift_off_z, const double *stance_time,
+                                         double com_height_nominal, double hip_height, double hip_offset, double gravity,
+                                         const double *com_pos_offset_b, int32_t reset_history, double *ref_feet) {
+    if (!h || !base_position || !base_ori_euler_xyz || !base_xy_lin_vel || !ref_base_xy_lin_vel || !hips_position ||
+        !lift_off_z || !stance_time) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t R = h->R;
+    const size_t n_d = R * (3 + 3 + 2 + 2 + 12 + 4 + 1 + 12 + 2 * FRG_HIST);
+    if (!h->d_frg) {
+        CK(cudaMalloc(&h->d_frg, n_d * sizeof(double) + R * 2 * sizeof(int)));
+        CK(cudaMemset(h->d_frg, 0, n_d * sizeof(double) + R * 2 * sizeof(int)));
+    }
+    double *d = (double *)h->d_frg;
+    double *d_pos = d, *d_eul = d_pos + 3 * R, *d_vel = d_eul + 3 * R, *d_rvel = d_vel + 2 * R, *d_hips = d_rvel + 2 * R,
+           *d_loz = d_hips + 12 * R, *d_st = d_loz + 4 * R, *d_feet = d_st + R, *d_hist = d_feet + 12 * R;
+    int *d_meta = (int *)(d_hist + 2 * FRG_HIST * R);
+    if (reset_history) CK(cudaMemsetAsync(d_meta, 0, R * 2 * sizeof(int), h->stream));
+    CK(cudaMemcpyAsync(d_pos, base_position, 3 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_eul, base_ori_euler_xyz, 3 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_vel, base_xy_lin_vel, 2 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_rvel, ref_base_xy_lin_vel, 2 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_hips, hips_position, 12 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_loz, lift_off_z, 4 * R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_st, stance_time, R * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    FrgParams fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.com_height_nominal = com_height_nominal; fp.hip_height = hip_height; fp.hip_offset = hip_offset; fp.gravity = gravity;
+    if (com_pos_offset_b) memcpy(fp.com_off_b, com_pos_offset_b, 3 * sizeof(double));
+    fp.R = (int)R;
+    const int threads = 64, blocks = (int)((R + threads - 1) / threads);
+    foothold_reference_kernel<<<blocks, threads, 0, h->stream>>>(fp, d_pos, d_eul, d_vel, d_rvel, d_hips, d_loz, d_st, d_hist,
+                                                                 d_meta, d_feet);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (ref_feet) {
+        CK(cudaMemcpyAsync(ref_feet, d_feet, 12 * R * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
     return QPMPC_OK;
 }
 

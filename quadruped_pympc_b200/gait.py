@@ -48,3 +48,30 @@ def contact_sequences_from_phase(controller, phase_signal, step_freq, duty_facto
         fr.ctypes.data_as(_DP), float(duty_factor), off.ctypes.data_as(_DP), dts.ctypes.data_as(_DP),
         lens.ctypes.data_as(C.POINTER(C.c_int32)), int(dts.size), None if out is None else out.ctypes.data_as(_lib._FP)))
     return out
+
+
+def footholds_reference(controller, base_position, base_ori_euler_xyz, base_xy_lin_vel, ref_base_xy_lin_vel, hips_position,
+                        lift_off_z, stance_time, com_height_nominal, hip_height, hip_offset=0.1, gravity=9.81,
+                        com_pos_offset_b=None, reset_history=False):
+    """`FootholdReferenceGenerator.compute_footholds_reference` (helpers/foothold_reference_generator.py:53-157) for the R
+    robots of `controller` in one launch, float64.  base_position / base_ori_euler_xyz (R,3), base_xy_lin_vel /
+    ref_base_xy_lin_vel (R,2), hips_position (R,4,3) in FL FR RL RR order, lift_off_z (R,4) = the z of each robot's
+    `frg.lift_off_positions`, stance_time (R,) or scalar.  The moving-average velocity history of each robot lives on the
+    device between calls (`reset_history=True` = freshly constructed generators).  Returns ref_feet (R,4,3), world frame."""
+    h = controller._ensure()
+    R = getattr(controller, 'num_robots', 1)
+
+    def arr(x, shape):
+        return np.ascontiguousarray(np.broadcast_to(np.asarray(x, np.float64), shape))
+
+    pos, eul = arr(np.reshape(base_position, (R, 3)), (R, 3)), arr(np.reshape(base_ori_euler_xyz, (R, 3)), (R, 3))
+    vel, rvel = arr(np.reshape(base_xy_lin_vel, (R, 2)), (R, 2)), arr(np.reshape(ref_base_xy_lin_vel, (R, 2)), (R, 2))
+    hips, loz = arr(np.reshape(hips_position, (R, 4, 3)), (R, 4, 3)), arr(np.reshape(lift_off_z, (R, 4)), (R, 4))
+    st = arr(stance_time, (R,))
+    off = None if com_pos_offset_b is None else arr(com_pos_offset_b, (3,))
+    out = np.empty((R, 4, 3), np.float64)
+    p = lambda a: a.ctypes.data_as(_DP)
+    _lib.check(_lib.load().qpmpc_footholds_reference(
+        h, p(pos), p(eul), p(vel), p(rvel), p(hips), p(loz), p(st), float(com_height_nominal), float(hip_height),
+        float(hip_offset), float(gravity), None if off is None else p(off), int(bool(reset_history)), p(out)))
+    return out
