@@ -190,6 +190,22 @@ int qpmpc_footholds_reference(qpmpc_handle *h, const double *base_position, cons
                               const double *hips_position, const double *lift_off_z, const double *stance_time,
                               double com_height_nominal, double hip_height, double hip_offset, double gravity,
                               const double *com_pos_offset_b, int32_t reset_history, double *ref_feet);
+/* MPC -> WBC output record: the 75-double shared-memory payload of ros2/run_controller.py:72-92
+ * (GRF 0..11 | footholds 12..23 | joints pos / vel / acc 24..59 | predicted state 60..71 | best_sample_freq 72 |
+ * last_mpc_loop_time 73 | stamp_mono 74) written under the reference's seqlock (:373-388: *seq odd while the payload is
+ * being written, even when stable; reader :587-602).  `record` = the SharedMemory buffer, `seq` = the 64-bit
+ * multiprocessing.Value('Q').  qpmpc_shm_pack packs caller-supplied values (no GPU, no handle): grfs (12) are multiplied
+ * by current_contact (4; NULL = ones) as interfaces/srbd_controller_interface.py:225-230 does, footholds (12 doubles;
+ * NULL = zeros) are the reference footholds the interface passes through (:170-175), the joint slots are NaN (the
+ * sampling controller returns None there and numpy stores None as NaN), predicted_state's first 12 entries are kept,
+ * the stamp is CLOCK_MONOTONIC seconds.  qpmpc_publish_shm does the same for robot `robot` of the handle straight from
+ * the pinned host packet the last tick / step landed in -- no Python objects between the kernel's result and the record. */
+#define QPMPC_SHM_DOUBLES 75
+int qpmpc_shm_pack(double *record, uint64_t *seq, const float *grfs, const float *current_contact,
+                   const double *footholds, const float *predicted_state, double best_sample_freq,
+                   double last_mpc_loop_time);
+int qpmpc_publish_shm(qpmpc_handle *h, int robot, double *record, uint64_t *seq, const float *current_contact,
+                      const double *footholds, double last_mpc_loop_time);
 /* Batched epilogue on the device-resident results of the last tick / step (all R robots of the handle):
  *   grfs_contact[r][3 leg + k] = GRFs * current_contact[leg]                  (srbd_controller_interface.py:225-230)
  *   tau[r][3 leg + j] = -(J_leg^T grfs_contact_leg)[j]                        (wb_interface.py:372-375)

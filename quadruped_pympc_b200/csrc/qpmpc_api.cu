@@ -12,6 +12,7 @@
 #include <cstddef>
 #include <cstdio>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -255,6 +256,7 @@ struct qpmpc_handle {
     int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
     float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet + stamp (host / device alias)
+    mutable const float *last_out = nullptr;      // pinned host packets of the last unpacked tick (qpmpc_publish_shm)
     unsigned int seq = 0;
     int lanes = 1;                    // 1: sample per thread ; 4: four lanes per sample (qpmpc_quad.cuh)
     unsigned long long *d_phase = nullptr;
@@ -564,6 +566,7 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
 static void unpack_one(const qpmpc_handle *h, int r, const float *base, qpmpc_tick_out *out) {
     const KParams &kp = h->kp;
     const float *rec = base + (size_t)r * kp.out_stride;
+    h->last_out = base;
     memcpy(out->grfs, rec + OUT_GRF, 12 * sizeof(float));
     memcpy(out->predicted_state, rec + OUT_PRED, 24 * sizeof(float));
     out->best_cost = rec[OUT_BESTCOST];
@@ -691,6 +694,46 @@ extern "C" int qpmpc_pgg_contact_sequence(qpmpc_handle *h, const double *phase_s
     }
     h->contacts_on_device = true;                          // the tick kernels of this stream run after the table kernel
     return QPMPC_OK;
+}
+
+// MPC -> WBC output record: the 75-double seqlock payload of ros2/run_controller.py:72-92, written
+// as the MPC process does at :373-388 (sequence odd while writing, even when stable), read at :587-602.
+enum { SHM_GRF = 0, SHM_FH = 12, SHM_JP = 24, SHM_JV = 36, SHM_JA = 48, SHM_PRED = 60, SHM_BSF = 72, SHM_LAST = 73, SHM_STAMP = 74 };
+extern "C" int qpmpc_shm_pack(double *record, uint64_t *seq, const float *grfs, const float *current_contact,
+                              const double *footholds, const float *predicted_state, double best_sample_freq,
+                              double last_mpc_loop_time) {
+    if (!record || !seq || !grfs || !predicted_state) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    const uint64_t s0 = __atomic_load_n(seq, __ATOMIC_RELAXED);
+    __atomic_store_n(seq, s0 | 1, __ATOMIC_RELAXED);                       // :374-376 (even -> s+1, odd stays)
+    __atomic_thread_fence(__ATOMIC_RELEASE);
+    const double nan = __builtin_nan("");
+    for (int leg = 0; leg < 4; ++leg) {
+        const double c = current_contact ? (double)current_contact[leg] : 1.0;     // interface :225-230 (float64 product)
+        for (int k = 0; k < 3; ++k) record[SHM_GRF + 3 * leg + k] = (double)grfs[3 * leg + k] * c;
+    }
+    for (int k = 0; k < 12; ++k) {
+        record[SHM_FH + k] = footholds ? footholds[k] : 0.0;               // ref_state feet, interface :170-175
+        // the sampling controller returns no joint trajectories (interface :178-180); numpy stores None as NaN (:380-382)
+        record[SHM_JP + k] = nan; record[SHM_JV + k] = nan; record[SHM_JA + k] = nan;
+        record[SHM_PRED + k] = (double)predicted_state[k];                 // first 12 of the 24, :383
+    }
+    record[SHM_BSF] = best_sample_freq;
+    record[SHM_LAST] = last_mpc_loop_time;
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);                                   // time.monotonic(), :386
+    record[SHM_STAMP] = (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+    __atomic_store_n(seq, (s0 | 1) + 1, __ATOMIC_RELEASE);                 // :388
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_publish_shm(qpmpc_handle *h, int robot, double *record, uint64_t *seq, const float *current_contact,
+                                 const double *footholds, double last_mpc_loop_time) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    if (robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "robot %d out of range", robot);
+    if (!h->last_out) return fail(QPMPC_ERR_INVALID, "no tick result on the host yet");
+    const float *rec = h->last_out + (size_t)robot * h->kp.out_stride;
+    return qpmpc_shm_pack(record, seq, rec + OUT_GRF, current_contact, footholds, rec + OUT_PRED, (double)rec[OUT_BESTFREQ],
+                          last_mpc_loop_time);
 }
 
 // layout of d_frg (doubles): base_pos 3R | euler 3R | vel 2R | ref vel 2R | hips 12R | lift_off_z 4R | stance R | feet 12R |
