@@ -144,6 +144,11 @@ int qpmpc_tick_iterations(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iter
  * srbd_controller_interface.py:128-129), then previous_contact <- contact_sequence[:, 0].  `out` = last iteration.
  * shift_solution is not supported here (config.py:194 default off). */
 int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, float sigma0, qpmpc_tick_out *out);
+/* shift_solution (mpc_params['shift_solution'], config.py:194) for the stateful controller: step > 0 makes every
+ * qpmpc_step* first write the carried best's spline value at `step` (= 1 / mpc_frequency, S:571-573) into knots [0], [2],
+ * [4] of every leg exactly as S:513-561 does, before the lift-off zeroing; 0 = off (default).  Refused for gait-adaptive
+ * handles (the reference's adaptive shift_solution raises, A:540-552). */
+int qpmpc_step_set_shift(qpmpc_handle *h, float step);
 /* (re)initialise the records: key = (seed, counter of the NEXT iteration), best (R x P) or NULL = zeros,
  * previous_contact (R x 4) or NULL = ones */
 int qpmpc_step_reset(qpmpc_handle *h, const uint32_t key[2], const float *best, const int32_t *previous_contact);

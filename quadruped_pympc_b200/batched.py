@@ -68,6 +68,7 @@ class BatchedSampling_MPC:
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
         self._stateful = False
+        self._shift_set = 0.0
         return h
 
     def close(self):
@@ -121,13 +122,17 @@ class BatchedSampling_MPC:
 
     # ------------------------------------------------------------------ stateful batch
     def step(self, states, references, contact_sequences, timing=None, nominal_step_frequency=None, optimize_swing=None,
-             iterations=1):
+             iterations=1, mpc_frequency=100):
         """The sampling block of SRBDControllerInterface.compute_control (I:118-168) for all R robots in one call, with
         every robot's best / sigma / key counter / previous contact kept on the device between calls: raw states in
-        (foothold substitution and lift-off zeroing happen in the kernel), `iterations` sampling iterations.
-        states (R,24) RAW, references (R,24), contact_sequences (R,4,>=H) -> like compute_control."""
+        (shift_solution when configured, foothold substitution and lift-off zeroing happen in the kernel), `iterations`
+        sampling iterations.  states (R,24) RAW, references (R,24), contact_sequences (R,4,>=H) -> like compute_control."""
         h = self._ensure()
         lib = _lib.load()
+        shift = 1.0 / mpc_frequency if self.cfg.shift_solution else 0.0       # S:571-573
+        if shift != self._shift_set:
+            _lib.check(lib.qpmpc_step_set_shift(h, shift))
+            self._shift_set = shift
         R, P, H = self.num_robots, self.num_control_parameters, self.horizon
         if not getattr(self, '_stateful', False):
             key = (C.c_uint32 * 2)(int(self.master_key[0]), (int(self.master_key[1]) + 1) & 0xFFFFFFFF)

@@ -256,6 +256,7 @@ struct qpmpc_handle {
     int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
     float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet + stamp (host / device alias)
+    float shift_step = 0.0f;                      // stateful controller: shift_solution step (1 / mpc_frequency), 0 = off
     mutable const float *last_out = nullptr;      // pinned host packets of the last unpacked tick (qpmpc_publish_shm)
     unsigned int seq = 0;
     int lanes = 1;                    // 1: sample per thread ; 4: four lanes per sample (qpmpc_quad.cuh)
@@ -908,6 +909,39 @@ extern "C" int qpmpc_step_state(qpmpc_handle *h, int robot, float *best, float *
     return QPMPC_OK;
 }
 
+// shift_solution for the stateful controller: index and basis of the spline at `step`, in numpy float32 order
+// (S:186-196 linear, S:209-225 cubic, S:265 zero-order); the kernel's staging applies them to the carried best.
+static void shift_basis(const qpmpc_handle *h, KParams &kp) {
+    const float step = h->shift_step;
+    const int H = h->H, ns = kp.ns;
+    kp.shift_kind = 1 + (int)h->cfg.parametrization;
+    if (h->cfg.parametrization == QPMPC_ZERO_ORDER) { kp.shift_index = (int)(int16_t)step; return; }
+    int index = 0;                                            // max(where(step >= linspace(0, H, ns + 1), arange, 0))
+    for (int k = 0; k <= ns; ++k) if (step >= kp.bounds[k] && k > index) index = k;
+    volatile float q = step / (float)((double)H / (double)ns) - (float)index;
+    kp.shift_index = index;
+    if (h->cfg.parametrization == QPMPC_LINEAR_SPLINE) { kp.shift_w[0] = 1.0f - q; kp.shift_w[1] = q; return; }
+    volatile float q2 = q * q, q3 = q2 * q;                   // q*q*q
+    volatile float tq = 2.0f * q, tq2 = tq * q, tq3 = tq2 * q;        // 2*q*q*q
+    volatile float hq = 3.0f * q, hq2 = hq * q;               // 3*q*q
+    volatile float mq = -2.0f * q, mq2 = mq * q, mq3 = mq2 * q;       // -2*q*q*q
+    volatile float a = tq3 - hq2, b = q3 - tq2;
+    kp.shift_w[0] = a + 1.0f;                                 // 2q^3 - 3q^2 + 1
+    kp.shift_w[1] = b + q;                                    // q^3 - 2q^2 + q
+    kp.shift_w[2] = mq3 + hq2;                                // -2q^3 + 3q^2
+    kp.shift_w[3] = q3 - q2;                                  // q^3 - q^2
+}
+
+extern "C" int qpmpc_step_set_shift(qpmpc_handle *h, float step) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    if (!(step >= 0.0f)) return fail(QPMPC_ERR_INVALID, "step must be >= 0");
+    if (step > 0.0f && h->cfg.adaptive) return fail(QPMPC_ERR_INVALID, "shift_solution: the gait-adaptive reference raises here (A:540-552)");
+    if (step > 0.0f && h->cfg.parametrization == QPMPC_ZERO_ORDER && (int)(int16_t)step >= h->H) return fail(QPMPC_ERR_INVALID, "step beyond the horizon");
+    if (step > 0.0f && h->cfg.parametrization != QPMPC_ZERO_ORDER && step >= (float)h->H) return fail(QPMPC_ERR_INVALID, "step beyond the horizon");
+    h->shift_step = step;
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, float sigma0, qpmpc_tick_out *out) {
     if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
     if (iterations < 1) return fail(QPMPC_ERR_INVALID, "iterations must be >= 1");
@@ -937,6 +971,8 @@ extern "C" int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iter
     }
     for (int it = 0; it < iterations; ++it) {
         kp.sigma_reset = (it == 0 && h->cfg.method == QPMPC_CEM_MPPI) ? 1 : 0;
+        kp.shift_kind = 0;
+        if (it == 0 && h->shift_step > 0.0f) shift_basis(h, kp);
         if (direct && it == iterations - 1) { kp.seq = 0; return direct_tick(h, kp, grid, out); }
         rc = launch(h, h->tick_fn, kp, grid);
         if (rc) return rc;

@@ -90,6 +90,9 @@ struct KParams {
     int ctrl_stride;
     int sigma_reset;                        // 1: this launch starts from sigma0 (I:128-129: reset at iteration 0 of every tick)
     float sigma0;
+    int shift_kind;                         // 0: off | 1 + PARAM: this launch first shifts the carried best (shift_solution,
+    int shift_index;                        //   S:513-561 from prepare_state_and_reference S:571-573): spline chunk / step
+    float shift_w[4];                       //   index and basis at step = 1/mpc_frequency, evaluated on the host
     uint32_t seed;                          // Philox counter word 3 of this launch (all robots of a batch share it)
     uint32_t robot_base;                    // global robot id = robot_base + blockIdx.y (< 2^23), part of counter word 0
     int peer_world;                         // > 1: the last block pushes its shard record into every peer's mailbox over

@@ -57,6 +57,31 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
             s.in[kp.off_best + k] = v;
         }
         __syncthreads();
+        if (kp.shift_kind) {        // shift_solution S:513-561: the spline value at `step` goes into knots [0], [2], [4] of every
+            if (threadIdx.x < 4) {  // leg (sic); numpy float32 arithmetic, no contraction.  One thread per leg.
+                float *p = s.in + kp.off_best + threadIdx.x * kp.P_leg;
+                const int i = kp.shift_index;
+                const float w0 = kp.shift_w[0], w1 = kp.shift_w[1], w2 = kp.shift_w[2], w3 = kp.shift_w[3];
+                float f[3];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    if (kp.shift_kind == 1) {                                   // zero-order, S:259-268
+                        f[a] = p[i + a * kp.H];
+                    } else if (kp.shift_kind == 2) {                            // linear, S:181-201
+                        const int o = i + (kp.ns + 1) * a;
+                        f[a] = __fadd_rn(__fmul_rn(w0, p[o]), __fmul_rn(w1, p[o + 1]));
+                    } else {                                                    // cubic, S:204-257
+                        const int o = 10 * i + 4 * a;
+                        const float p0 = p[o], p1 = p[o + 1], p2 = p[o + 2], p3 = p[o + 3];
+                        const float phi = __fmul_rn(0.5f, __fadd_rn(__fsub_rn(p2, p1), __fsub_rn(p1, p0)));
+                        const float phin = __fmul_rn(0.5f, __fadd_rn(__fsub_rn(p3, p2), __fsub_rn(p2, p1)));
+                        f[a] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(w0, p1), __fmul_rn(w1, phi)), __fmul_rn(w2, p2)), __fmul_rn(w3, phin));
+                    }
+                }
+                p[0] = f[0]; p[2] = f[1]; p[4] = f[2];
+            }
+            __syncthreads();
+        }
         const unsigned int prev = __float_as_uint(__ldcg(st + 2 * kp.P + 1));
         if (threadIdx.x == 0) s.in[IN_TICK] = __ldcg(st + 2 * kp.P);
         if (threadIdx.x < 12) {                                   // swing feet <- reference footholds, S:588-595

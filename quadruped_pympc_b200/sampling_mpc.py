@@ -208,6 +208,7 @@ class Sampling_MPC:
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
         self._stateful = False                                  # a new handle starts without a device record
+        self._shift_set = 0.0
         self._n_local = lib.qpmpc_num_local_samples(h)
         self._buf = _TickBuffers(self.num_control_parameters, self.elite_k, self.horizon)
         return h
@@ -445,19 +446,21 @@ class Sampling_MPC:
                  "ref_foot_FL", "ref_foot_FR", "ref_foot_RL", "ref_foot_RR")
 
     def step(self, state_current, ref_state, contact_sequence, pgg_phase_signal=None, pgg_step_freq=None,
-             optimize_swing=0, iterations=None):
+             optimize_swing=0, iterations=None, mpc_frequency=100):
         """The sampling block of SRBDControllerInterface.compute_control (I:118-168) in ONE call:
 
             prepare_state_and_reference(...); previous_contact_mpc = current_contact
             for _ in range(num_sampling_iterations): with_newkey(); [with_newsigma(cfg sigma) at 0]; jitted_compute_control(...)
 
         with best_control_parameters, sigma, the key counter and previous_contact_mpc kept in a device record between
-        calls (the foothold substitution and the lift-off knot zeroing happen in the kernel's staging).  `state_current`
+        calls (shift_solution, the foothold substitution and the lift-off knot zeroing happen in the kernel's staging).  `state_current`
         / `ref_state` are the interface's dicts (or raw 24-vectors).  Returns the last iteration's tuple; the host
         mirrors (`best_control_parameters`, `master_key`, `sigma_cem_mppi`) are kept in step."""
-        if self.cfg.shift_solution:
-            raise _lib.QpmpcError(_lib.ERR_INVALID, 'step(): shift_solution is not supported by the stateful controller')
         h, lib, b = self._ensure(), _lib.load(), self._buf
+        shift = 1.0 / mpc_frequency if self.cfg.shift_solution else 0.0       # S:571-573, done in the kernel's staging
+        if shift != getattr(self, '_shift_set', 0.0):
+            _lib.check(lib.qpmpc_step_set_shift(h, shift))
+            self._shift_set = shift
         n = self.num_sampling_iterations if iterations is None else int(iterations)
         if isinstance(state_current, dict):
             st = np.concatenate([np.asarray(state_current[k], np.float64).reshape(-1) for k in self._STATE_KEYS])

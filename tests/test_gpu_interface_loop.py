@@ -166,3 +166,61 @@ def test_stateful_step_equals_the_interface_block(built, method, adaptive, iters
         np.testing.assert_array_equal(pc, current_contact.astype(int))
         assert key[1] == host.master_key[1] + 1
     assert saw_liftoff
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('param', ['zero_order', 'linear_spline', 'cubic_spline'])
+@pytest.mark.parametrize('method,lanes', [('mppi', 1), ('cem_mppi', 4), ('random_sampling', 1)])
+def test_stateful_step_with_shift_solution(built, param, method, lanes):
+    """mpc_params['shift_solution'] = True (config.py:194 has False): the shift of the carried best (S:513-561, called from
+    prepare_state_and_reference S:571-573) done in the kernel's staging must equal the host-driven block bit for bit,
+    single and batched, 2 sampling iterations (the shift applies once per tick, before iteration 0)."""
+    from quadruped_pympc_b200.batched import BatchedSampling_MPC
+    kw = dict(sampling_method=method, control_parametrization=param, num_parallel_computations=1500,
+              num_sampling_iterations=2, lanes_per_sample=lanes, shift_solution=True)
+    cem = method == 'cem_mppi'
+    cfg = qp.SamplerConfig.for_robot('go2', **kw)
+    host, dev, bat = qp.Sampling_MPC(cfg), qp.Sampling_MPC(cfg), BatchedSampling_MPC(cfg, 3)
+    previous_contact_mpc = np.array([1, 1, 1, 1])
+    for tick in range(5):
+        sc = synthetic.scenario('go2', 'trot', seed=60 + tick, sim_steps=45 * tick)
+        state_current, ref_state = _dicts(sc)
+        contact_sequence = sc['contact_sequence']
+        current_contact = contact_sequence[:, 0].copy()
+        before = host.best_control_parameters.copy()
+        state_jax, ref_jax = host.prepare_state_and_reference(state_current, ref_state, current_contact, previous_contact_mpc)
+        if tick > 0:
+            assert not np.array_equal(before, host.best_control_parameters)         # the shift did something
+        previous_contact_mpc = current_contact
+        for it in range(2):
+            host.with_newkey()
+            if cem and it == 0:
+                host.with_newsigma(host.cfg.sigma_cem_mppi)
+            args = ((host.sigma_cem_mppi,) if cem else ()) + (sc['phase_signal'], sc['nominal_step_freq'], 1)
+            out_h = host.jitted_compute_control(state_jax, ref_jax, contact_sequence, host.best_control_parameters,
+                                                host.master_key, *args)
+            host.best_control_parameters = out_h[3]
+            if cem:
+                host.with_newsigma(out_h[7])
+        out_d = dev.step(state_current, ref_state, contact_sequence, sc['phase_signal'], sc['nominal_step_freq'], 1)
+        for a, b in zip(out_h[:6], out_d[:6]):
+            np.testing.assert_array_equal(np.asarray(a), np.asarray(b))
+        # batched: robot 0 of the batch has robot id 0 = the single controller's stream
+        raw = np.concatenate([np.asarray(state_current[k], np.float64).reshape(-1) for k in qp.Sampling_MPC._STATE_KEYS])
+        rf = np.concatenate([np.asarray(ref_state[k], np.float64).reshape(-1)[:3] for k in qp.Sampling_MPC._REF_KEYS])
+        out_b = bat.step(np.tile(raw, (3, 1)), np.tile(rf, (3, 1)), np.tile(contact_sequence[None], (3, 1, 1)),
+                         timing=np.tile(np.asarray(sc['phase_signal'], np.float32), (3, 1)),
+                         nominal_step_frequency=sc['nominal_step_freq'], optimize_swing=1, iterations=2)
+        np.testing.assert_array_equal(out_b[0][0], np.asarray(out_h[0]))
+        np.testing.assert_array_equal(out_b[2][0], np.asarray(out_h[3]))
+
+
+@pytest.mark.gpu
+def test_shift_is_refused_for_the_gait_adaptive_controller(built):
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=512, optimize_step_freq=True,
+                                     shift_solution=True)
+    ctrl = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario('go2', 'trot', seed=1)
+    state_current, ref_state = _dicts(sc)
+    with pytest.raises(Exception):
+        ctrl.step(state_current, ref_state, sc['contact_sequence'], sc['phase_signal'], sc['nominal_step_freq'], 1)
