@@ -82,7 +82,9 @@ typedef struct qpmpc_config {
     float pgg_duty_factor;        /* 0.65 hard-coded in A:179 */
     int32_t robot_base;           /* global id of this handle's robot 0 (robot-partitioned multi-GPU runs; Philox key word 1) */
     int32_t lanes_per_sample;     /* kernel variant: 1 = one sample per thread (throughput), 4 = four lanes per sample, one
-                                     leg each (latency: one controller at ~10k samples), 0 = choose by samples per launch */
+                                     leg each (latency: one small controller), 14 = one sample per thread plus three
+                                     noise-helper threads per sample (latency: one controller of up to 148 x 128 samples;
+                                     falls back to 1 when the launch does not qualify), 0 = choose by samples per launch */
 } qpmpc_config;
 
 /* One robot's inputs for one tick = the arguments of jitted_compute_control (I:140-168) */

@@ -190,13 +190,13 @@ __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
 // ------------------------------------------------------------------------------------------------------
 // kernel dispatch tables (parametrisation x adaptive x method)
 // ------------------------------------------------------------------------------------------------------
-static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3];
+static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3];
 static void fill_kernel_tables() {
     static bool done = false;
     if (done) return;
-    qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER]);
-    qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR]);
-    qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC]);
+    qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER], g_tick_h_table[ZERO_ORDER]);
+    qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR], g_tick_h_table[LINEAR]);
+    qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC], g_tick_h_table[CUBIC]);
     qp_inst_quad_zero(g_quad_table[ZERO_ORDER]);
     qp_inst_quad_linear(g_quad_table[LINEAR]);
     qp_inst_quad_cubic(g_quad_table[CUBIC]);
@@ -254,6 +254,7 @@ struct qpmpc_handle {
     NcclComm comm = nullptr;
     KernelFn tick_fn = nullptr, finish_fn = nullptr;
     int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
+    bool helpers = false;             // tick_fn = tick_kernel_h (sample per thread + noise helper threads)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
     float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet + stamp (host / device alias)
     float shift_step = 0.0f;                      // stateful controller: shift_solution step (1 / mpc_frequency), 0 = off
@@ -416,9 +417,12 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     // Kernel choice: the four-lanes-per-sample kernel wins while the GPU is under-filled (few samples in flight: one
     // controller at 10k samples), the sample-per-thread kernel executes ~1.8x fewer instructions per sample and wins
     // once its warps fill the machine.  lanes_per_sample = 0 picks by the number of samples of one launch.
-    if (cfg->lanes_per_sample != 0 && cfg->lanes_per_sample != 1 && cfg->lanes_per_sample != 4) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1 or 4"); }
-    h->lanes = cfg->lanes_per_sample ? cfg->lanes_per_sample : ((long long)h->n_local * h->R <= QPMPC_QUAD_MAX_SAMPLES ? 4 : 1);
+    const int lps = cfg->lanes_per_sample;
+    if (lps != 0 && lps != 1 && lps != 4 && lps != 14) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1, 4 or 14"); }
+    h->lanes = lps == 4 ? 4 : (lps != 0 ? 1 : ((long long)h->n_local * h->R <= QPMPC_QUAD_MAX_SAMPLES ? 4 : 1));
     plan_blocks(h->n_local, h->lanes, &kp.iters, &kp.nblk);
+    // sample per thread + noise helper threads (tick_kernel_h): one controller, one tile per block, no more blocks than SMs
+    h->helpers = (h->lanes == 1 && lps != 1 && h->R == 1 && kp.iters == 1 && kp.nblk <= 148);
     kp.elite_k = elite_k;
     kp.mode = MODE_TICK; kp.noise_mode = NOISE_PHILOX; kp.freq_injected = 0;
     kp.fused_finish = (W == 1); kp.world = W; kp.carry_best = 0;
@@ -460,7 +464,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
             kp.basis[n][0] = 1.0f - q; kp.basis[n][1] = q;
         }
     }
-    h->threads = h->lanes == 4 ? QTB : TB;
+    h->threads = h->lanes == 4 ? QTB : (h->helpers ? TB * NOISE_HELPERS : TB);
     h->finish_smem_bytes = smem_floats(kp.in_stride, h->P) * sizeof(float);
     if (h->lanes == 4)      // the CEM elite refit of finish() stages up to `threads` noise rows in the tile
         h->smem_bytes = smem_floats(kp.in_stride, h->P, QTB, cfg->method == QPMPC_CEM_MPPI ? QTB + 1 : QTS) * sizeof(float);
@@ -469,7 +473,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     if (h->smem_bytes > 227 * 1024) { delete h; return fail(QPMPC_ERR_INVALID, "tile of %d knots needs %zu B shared memory (> 227 KB)", h->P, h->smem_bytes); }
 
     fill_kernel_tables();
-    h->tick_fn = (h->lanes == 4 ? g_quad_table : g_tick_table)[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    h->tick_fn = (h->lanes == 4 ? g_quad_table : (h->helpers ? g_tick_h_table : g_tick_table))[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));

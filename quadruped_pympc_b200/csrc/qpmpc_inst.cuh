@@ -1,5 +1,5 @@
 // qpmpc_inst.cuh -- explicit instantiation units.  The 3 x 2 x 3 (parametrisation x adaptive x method) variants of the
-// two tick kernels are compiled in six translation units (inst_*.cu) so that the build parallelises; qpmpc_api.cu
+// tick kernels (sample per thread, the same with noise helper threads, four lanes per sample) are compiled in six translation units (inst_*.cu) so that the build parallelises; qpmpc_api.cu
 // collects the function pointers through these accessors.
 #pragma once
 #include "qpmpc_kernels.cuh"
@@ -9,9 +9,9 @@ typedef void (*KernelFn)(const KParams);
 }
 
 extern "C" {
-void qp_inst_tick_zero(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3]);
-void qp_inst_tick_linear(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3]);
-void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3]);
+void qp_inst_tick_zero(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
+void qp_inst_tick_linear(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
+void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
 void qp_inst_quad_zero(qp::KernelFn quad[2][3]);
 void qp_inst_quad_linear(qp::KernelFn quad[2][3]);
 void qp_inst_quad_cubic(qp::KernelFn quad[2][3]);

@@ -535,21 +535,28 @@ __device__ __forceinline__ void after_shard_reduce(const KParams &kp, int r, con
 // ======================================================================================================
 // The tick kernel.  grid = (nblk, R), block = TB.  dynamic smem = smem_floats(...) * 4 bytes.
 // ======================================================================================================
-template <int PARAM, bool ADAPTIVE, int METHOD>
-__global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KParams kp) {
+//
+// NH > 1 (tick_kernel_h, one controller whose samples fit one tile per block on <= 148 blocks): the block carries NH - 1
+// extra groups of TB "noise helper" threads.  At 10k samples the machine is under-filled (one warp per scheduler on half
+// the SMs) and the Philox / Box-Muller phase is a serial chain of P/4 quads per thread; helper group h draws quads
+// h, h + NH, ... of the same sample column into the tile, then exits (barriers after that point count the non-exited
+// threads only).  Same Philox counters, same tile contents: results are bit-identical to NH = 1.
+template <int PARAM, bool ADAPTIVE, int METHOD, int NH>
+__device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     extern __shared__ __align__(16) float smem_raw[];
     const Smem s(smem_raw, kp);
-    const int t = threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
-    __shared__ int s_last;
+    const int t = NH > 1 ? (int)(threadIdx.x & (TB - 1)) : (int)threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
+    const int hlp = NH > 1 ? (int)(threadIdx.x / TB) : 0;
     if (blk == 0) phase_mark(kp, 0);
-    stage_inputs<TB>(kp, r, s);
+    stage_inputs<TB * NH>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
     const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + t;
     float m_run = CUDART_INF_F, s_run = 0.0f;
     int idx_run = 0x7fffffff;
-    for (int p = t; p < kp.P; p += TB) s.v[p] = 0.0f;
+    if (hlp == 0)
+        for (int p = t; p < kp.P; p += TB) s.v[p] = 0.0f;
 
     for (int it = 0; it < kp.iters; ++it) {
         const int tile_base = (blk * kp.iters + it) * TB;       // local (shard) index of this tile's first sample
@@ -561,7 +568,7 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         if (kp.noise_mode == NOISE_INJECTED) {
             const int rows = (kp.n_local - tile_base) < TB ? (kp.n_local - tile_base) : TB;
             const float *src = kp.noise + ((size_t)r * kp.N + kp.sample_base + tile_base) * kp.P;
-            for (int e = t; e < TB * kp.P; e += TB) {
+            for (int e = threadIdx.x; e < TB * kp.P; e += TB * NH) {
                 const int row = e / kp.P, p = e - row * kp.P;
                 s.tile[p * TS + row] = row < rows ? __ldg(src + e) : 0.0f;
             }
@@ -569,16 +576,18 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
         } else {
             if (active && gi != 0) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
-                float *tp = tcol;
+                float *tp = tcol + hlp * 4 * TS;
 #pragma unroll 4
-                for (int q = 0; q < kp.P / 4; ++q, tp += 4 * TS) {
+                for (int q = hlp; q < kp.P / 4; q += NH, tp += NH * 4 * TS) {
                     const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
                     tp[0] = e.x; tp[TS] = e.y; tp[2 * TS] = e.z; tp[3 * TS] = e.w;
                 }
             } else {                                            // padding rows and row 0 (the previous best re-evaluated)
-                for (int p = 0; p < kp.P; ++p) tcol[p * TS] = 0.0f;
+                for (int p = hlp; p < kp.P; p += NH) tcol[p * TS] = 0.0f;
             }
+            if (NH > 1) __syncthreads();                        // the helpers' quads are in the tile
         }
+        if (NH > 1 && hlp > 0) return;                          // single tile per block (host: iters == 1): helpers are done
         if (blk == 0 && it == 0) phase_mark(kp, 2);
         // ---- 2. rollout + cost ----
         float cost = CUDART_INF_F;
@@ -647,6 +656,19 @@ __global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KPa
     after_shard_reduce<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 11);
     if (t == 0) kp.counters[r] = 0u;
+}
+
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__global__ void __launch_bounds__(TB, 4) tick_kernel(const __grid_constant__ KParams kp) {
+    __shared__ int s_last;
+    tick_body<PARAM, ADAPTIVE, METHOD, 1>(kp, s_last);
+}
+
+constexpr int NOISE_HELPERS = 4;            // thread groups per block of tick_kernel_h (one computes, three only draw noise)
+template <int PARAM, bool ADAPTIVE, int METHOD>
+__global__ void __launch_bounds__(TB * NOISE_HELPERS, 1) tick_kernel_h(const __grid_constant__ KParams kp) {
+    __shared__ int s_last;
+    tick_body<PARAM, ADAPTIVE, METHOD, NOISE_HELPERS>(kp, s_last);
 }
 
 // Step 6 alone: merges `world` gathered shard records (sample-sharded controllers).  grid = (1, R).

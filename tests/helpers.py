@@ -11,7 +11,7 @@ KNOT_RTOL = 1e-4      # returned GRFs / knots (plus a small absolute floor for v
 
 PARAMS = ['zero_order', 'linear_spline', 'cubic_spline']
 METHODS = ['random_sampling', 'mppi', 'cem_mppi']
-LANES = [1, 4]      # kernel variants: sample per thread | four lanes per sample
+LANES = [1, 4, 14]  # kernel variants: sample per thread | four lanes per sample | sample per thread + noise helpers
 
 
 def make_pair(robot='go2', N=1000, **kw):

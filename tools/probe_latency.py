@@ -92,22 +92,22 @@ if __name__ == '__main__':
         ms, ph = resident(lanes=int(what[3]), steps=10)
         print(f'config2 lanes={what[3]}: kernel {ms * 1e3:.1f} us | {fmt_phases(ph)}', flush=True)
     if what in ('quick', 'phases'):
-        for lanes in (1, 4):
+        for lanes in (1, 14, 4):
             ms, ph = resident(lanes=lanes)
             print(f'config2 lanes={lanes}: kernel {ms * 1e3:.1f} us | {fmt_phases(ph)}', flush=True)
-        for lanes in (1, 4):
+        for lanes in (1, 14, 4):
             ms, ph = resident(method='random_sampling', param='zero_order', robot='aliengo', lanes=lanes)
             print(f'config1 lanes={lanes}: kernel {ms * 1e3:.1f} us | {fmt_phases(ph)}', flush=True)
         for lanes in (1, 4):
             ms, ph = resident(method='cem_mppi', N=50000, adaptive=True, robot='hyqreal1', lanes=lanes, steps=20)
             print(f'config3 lanes={lanes}: kernel {ms * 1e3:.1f} us | {fmt_phases(ph)}', flush=True)
     if what in ('quick', 'sweep'):
-        for N in (1000, 4000, 10000, 20000, 40000, 100000, 1000000):
+        for N in (1000, 2000, 4000, 6000, 8000, 10000, 14000, 18000, 20000, 40000, 100000, 1000000):
             row = []
-            for lanes in (1, 4):
-                ms, _ = resident(N=N, lanes=lanes, steps=20)
+            for lanes in (1, 4, 14):            # 14 = sample per thread + noise helpers (falls back to 1 above 148 tiles)
+                ms, _ = resident(N=N, lanes=lanes, steps=30)
                 row.append(ms * 1e3)
-            print(f'N={N:8d}  R=1   lanes1 {row[0]:9.1f} us   lanes4 {row[1]:9.1f} us', flush=True)
+            print(f'N={N:8d}  R=1   lanes1 {row[0]:9.1f} us   lanes4 {row[1]:9.1f} us   lanes14 {row[2]:9.1f} us', flush=True)
         for R in (2, 8, 32, 128, 512):
             row = []
             for lanes in (1, 4):
@@ -115,7 +115,7 @@ if __name__ == '__main__':
                 row.append(ms * 1e3)
             print(f'N=   10000  R={R:<4d} lanes1 {row[0]:9.1f} us   lanes4 {row[1]:9.1f} us', flush=True)
     if what in ('quick', 'e2e'):
-        for lanes in (1, 4):
+        for lanes in (1, 14, 4):
             e2e(lanes=lanes)
         e2e(lanes=1, io_mode='memcpy')
         e2e(lanes=1, io_mode='memcpy', use_graph=False)
