@@ -118,7 +118,25 @@ template <int METHOD, int NT>
 __device__ void merge_records(const float *recs, int n, size_t stride, int P, const Smem &s, float &M, int &IDX, float &S,
                               const KParams *dbg = nullptr) {
     constexpr int TB = NT;
+    constexpr int PF = 16;                                 // V rows per thread fetched ahead of the (min, argmin) reduction
     const int t = threadIdx.x;
+    // The V rows do not depend on M: their loads go out first so that their L2 round trip overlaps the one of the
+    // (m, idx) loads and the block reduction instead of following it (single tick: 79 records, one serial chain less).
+    const int nc = P >> 2;
+    const bool fast = METHOD != RANDOM_SAMPLING && (P & 3) == 0 && nc <= TB && (stride & 3) == 0;
+    const int G = fast ? TB / nc : 1;
+    const int g = fast ? t / nc : 0, c4 = fast ? t - g * nc : 0;
+    const size_t stride4 = stride >> 2;
+    float4 pv[PF];
+    if (fast) {
+        const float4 *col = reinterpret_cast<const float4 *>(recs + REC_V) + c4;
+        const int cnt0 = n < TB ? n : TB;
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int k = g + u * G;
+            pv[u] = (g < G && k < cnt0) ? col[(size_t)k * stride4] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
     float c = CUDART_INF_F;
     int i = 0x7fffffff;
     for (int b = t; b < n; b += TB) {
@@ -133,11 +151,7 @@ __device__ void merge_records(const float *recs, int n, size_t stride, int P, co
     // Fast path (P % 4 == 0, P/4 <= TB: every default configuration): float4 loads of the V rows, the records split
     // over G = TB / (P/4) thread groups (independent coalesced loads in flight instead of one serial chain per knot),
     // group partials combined in a fixed order -> deterministic.
-    const int nc = P >> 2;
-    if ((P & 3) == 0 && nc <= TB && (stride & 3) == 0) {
-        const int G = TB / nc;
-        const int g = t / nc, c4 = t - g * nc;
-        const size_t stride4 = stride >> 2;
+    if (fast) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int base = 0; base < n; base += TB) {
             const int b = base + t;
@@ -154,8 +168,19 @@ __device__ void merge_records(const float *recs, int n, size_t stride, int P, co
             const int cnt = (n - base) < TB ? (n - base) : TB;
             if (g < G) {
                 const float4 *col = reinterpret_cast<const float4 *>(recs + (size_t)base * stride + REC_V) + c4;
+                int k_first = g;
+                if (base == 0) {                                 // the prefetched rows, same record order
+#pragma unroll
+                    for (int u = 0; u < PF; ++u) {
+                        const int k = g + u * G;
+                        const float w = k < cnt ? s.w[k] : 0.0f;
+                        acc.x = fmaf(w, pv[u].x, acc.x); acc.y = fmaf(w, pv[u].y, acc.y);
+                        acc.z = fmaf(w, pv[u].z, acc.z); acc.w = fmaf(w, pv[u].w, acc.w);
+                    }
+                    k_first = g + PF * G;
+                }
                 // eight independent 16-byte loads in flight per thread, then the FMAs in record order
-                for (int k0 = g; k0 < cnt; k0 += 8 * G) {
+                for (int k0 = k_first; k0 < cnt; k0 += 8 * G) {
                     float4 v[8];
                     float w[8];
 #pragma unroll

@@ -16,7 +16,7 @@ if timeout 300 $CMD > gpurun_out/plain_$TAG.log 2>&1; then
   echo "ncu full rc=$?"
   # ... and the batched throughput launch (512 robots x 10k)
   CMDB="python bench.py --steps 6 --warmup 3 --multi-robots 512 --no-cpu-baseline --no-sweep"
-  timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^tick_kernel$" -s 20 -c 1 -f -o gpurun_out/prof_batched_$TAG $CMDB > gpurun_out/ncu_full_batched_$TAG.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^tick_kernel$" -s 2 -c 1 -f -o gpurun_out/prof_batched_$TAG $CMDB > gpurun_out/ncu_full_batched_$TAG.log 2>&1
   echo "ncu full batched rc=$?"
 else
   echo "plain run failed"; tail -20 gpurun_out/plain_$TAG.log
