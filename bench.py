@@ -424,6 +424,7 @@ def main():
     kernel_ms = float(ms.mean())
     achieved_tf = R * FLOP_PER_TICK / (kernel_ms * 1e-3) / 1e12
     hbm_bytes = R * (4 * (60 + 4 * HORIZON + 2 * P_KNOTS) + 4 * N_SAMPLES + 4 * (40 + 2 * P_KNOTS))
+    kernel_name = lib.qpmpc_kernel_name(h).decode()      # the variant qpmpc_create picked for this launch shape
     lib.qpmpc_destroy(h)
 
     # ---- e2e through the public API with host buffers (rank-local controller; aggregate = world x) -----------
@@ -489,7 +490,7 @@ def main():
             'gpu_launches': launches + e2e_launches,
             'roofline': {'bound': 'fp32', 'achieved': achieved_tf, 'peak': fp32_peak, 'unit': 'TFLOP/s',
                          'frac': achieved_tf / fp32_peak, 'traffic': ncu_traffic_bytes(),
-                         'kernel': 'qp::tick_kernel<CUBIC,false,MPPI>', 'kernel_ms': kernel_ms,
+                         'kernel': f'qp::{kernel_name}<CUBIC,false,MPPI>', 'kernel_ms': kernel_ms,
                          'algorithmic_flop_per_launch': R * FLOP_PER_TICK,
                          'peak_source': 'FP32 FMA microbenchmark measured in this process (MEASURED_PEAKS.json has no '
                                         'FP32 CUDA-core figure); latency-bound at 10k samples, see multi_robot.roofline',

@@ -128,6 +128,7 @@ int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out);   /* replaces Sam
 void qpmpc_destroy(qpmpc_handle *h);
 int qpmpc_num_parameters(const qpmpc_handle *h);          /* P = num_control_parameters, S:52-93 */
 int qpmpc_num_local_samples(const qpmpc_handle *h);       /* samples evaluated by this shard */
+const char *qpmpc_kernel_name(const qpmpc_handle *h);     /* tick kernel variant the handle launches (lanes_per_sample) */
 
 /* ---- the tick: replaces Sampling_MPC.jitted_compute_control (S:112, called at I:140/159) ------------- */
 int qpmpc_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);

@@ -936,6 +936,11 @@ static void shift_basis(const qpmpc_handle *h, KParams &kp) {
     kp.shift_w[3] = q3 - q2;                                  // q^3 - q^2
 }
 
+extern "C" const char *qpmpc_kernel_name(const qpmpc_handle *h) {
+    if (!h) return "";
+    return h->lanes == 4 ? "tick_kernel_quad" : (h->helpers ? "tick_kernel_h" : "tick_kernel");
+}
+
 extern "C" int qpmpc_step_set_shift(qpmpc_handle *h, float step) {
     if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
     if (!(step >= 0.0f)) return fail(QPMPC_ERR_INVALID, "step must be >= 0");

@@ -213,6 +213,11 @@ class Sampling_MPC:
         self._buf = _TickBuffers(self.num_control_parameters, self.elite_k, self.horizon)
         return h
 
+    @property
+    def kernel_name(self):
+        """tick kernel variant this controller launches (tick_kernel | tick_kernel_h | tick_kernel_quad)"""
+        return _lib.load().qpmpc_kernel_name(self._ensure()).decode()
+
     def close(self):
         if self._handle is not None and self._pid == os.getpid():
             _lib.load().qpmpc_destroy(self._handle)

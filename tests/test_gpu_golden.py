@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 FIXTURES = tick_fixtures()
 
 
-@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('lanes', [1, 4, 14])
 @pytest.mark.parametrize('path', FIXTURES, ids=fixture_id)
 def test_cuda_tick_reproduces_reference(built, path, lanes):
     fx = Fixture(path)
@@ -45,7 +45,7 @@ def test_cuda_tick_reproduces_reference(built, path, lanes):
         np.testing.assert_allclose(out[7], exp['new_sigma_cem_mppi'], rtol=KNOT_RTOL, atol=1e-6)
 
 
-@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('lanes', [1, 4, 14])
 @pytest.mark.parametrize('path', FIXTURES, ids=fixture_id)
 def test_cuda_rollout_seam_reproduces_reference(built, path, lanes):
     """jit_vectorized_rollout (S:176-177 / A:186-187): explicit parameters in, raw costs out."""

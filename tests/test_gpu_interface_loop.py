@@ -80,7 +80,7 @@ def test_interface_tick_loop(built, method):
         assert np.all(np.array(nmpc_GRFs).reshape(4, 3)[current_contact == 0] == 0)
 
 
-@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('lanes', [1, 4, 14])
 @pytest.mark.parametrize('method,adaptive', [('random_sampling', False), ('mppi', False), ('cem_mppi', False),
                                              ('mppi', True), ('cem_mppi', True)])
 def test_device_resident_sampling_iterations_equal_the_host_loop(built, method, adaptive, lanes):
@@ -118,7 +118,7 @@ def test_device_resident_sampling_iterations_equal_the_host_loop(built, method, 
     assert host.last_best_index == dev.last_best_index
 
 
-@pytest.mark.parametrize('lanes', [1, 4])
+@pytest.mark.parametrize('lanes', [1, 4, 14])
 @pytest.mark.parametrize('method,adaptive,iters', [('random_sampling', False, 1), ('mppi', False, 3), ('cem_mppi', False, 2),
                                                    ('mppi', True, 2), ('cem_mppi', True, 1)])
 def test_stateful_step_equals_the_interface_block(built, method, adaptive, iters, lanes):

@@ -118,3 +118,32 @@ def test_device_noise_matches_host_mirror(built, method):
         assert abs(z.mean()) < 5e-3 and abs(z.std() - 1) < 5e-3
         assert abs(np.mean(z ** 4) - 3.0) < 0.05                  # kurtosis of a normal
         assert abs(np.corrcoef(z[:, 0], z[:, 1])[0, 1]) < 0.05    # the two Box-Muller outputs are uncorrelated
+
+
+@pytest.mark.parametrize('method', METHODS)
+@pytest.mark.parametrize('N', [1, 2, 127, 129, 1000, 18944, 18945])
+def test_kernel_variants_agree_bit_for_bit_on_ragged_sizes(built, method, N):
+    """Production mode (in-kernel Philox): sample per thread, the same with noise-helper threads (one tile per block on
+    <= 148 blocks: N <= 18 944, otherwise it IS the plain kernel) and four lanes per sample draw the same rows and must
+    return the same tick, also when the last tile is ragged or holds only the zero-noise row."""
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200 import synthetic
+    sc = synthetic.scenario('go2', 'trot', seed=11)
+    outs, keep = [], []
+    for lanes in (1, 14, 4):
+        cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='cubic_spline',
+                                         num_parallel_computations=N, lanes_per_sample=lanes)
+        ctrl = qp.Sampling_MPC(cfg)
+        keep.append(ctrl)                                 # costs are fetched lazily from the live handle
+        best = np.linspace(-1, 1, ctrl.num_control_parameters).astype(np.float32)
+        args = (np.full(ctrl.num_control_parameters, 2.0, np.float32),) if method == 'cem_mppi' else ()
+        ctrl.with_newkey()
+        outs.append(ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best, ctrl.master_key,
+                                                *args, sc['phase_signal'], sc['nominal_step_freq'], 1))
+        assert ctrl.last_best_index < N
+    for o in outs[1:2]:                                   # helpers: bit-identical to the plain kernel
+        for a, b in zip(outs[0], o):
+            np.testing.assert_array_equal(np.asarray(a), np.asarray(b))
+    # four lanes: a different summation order inside the rollout -> FP32 tolerance of the north_star
+    np.testing.assert_allclose(np.asarray(outs[2][6]), np.asarray(outs[0][6]), rtol=3 * COST_RTOL)
+    np.testing.assert_allclose(np.asarray(outs[2][0]), np.asarray(outs[0][0]), rtol=1e-4, atol=1e-3)
