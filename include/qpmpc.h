@@ -278,6 +278,9 @@ int qpmpc_kernel_launch_count(const qpmpc_handle *h, uint64_t *count); /* kernel
  * (start, inputs staged, noise drawn, rollouts done, tile reduced, record published); out[8..11]: the last block of robot
  * 0 (ticket taken, block records merged, -, result packet written).  Slots never reached stay 0. */
 int qpmpc_debug_phase_times(qpmpc_handle *h, uint64_t out[16]);
+/* host-side timeline of the last direct-I/O tick (CLOCK_MONOTONIC ns): call entered, kernel launched, result stamp
+ * seen, result unpacked.  enable != 0 switches the four clock reads on for the following ticks; out may be NULL. */
+int qpmpc_debug_host_times(qpmpc_handle *h, int32_t enable, uint64_t out[4]);
 /* FP32 FMA peak of the device (dependent-free FFMA streams on every SM), TFLOP/s; sm_mhz may be NULL */
 int qpmpc_measure_fp32_peak(int device, float *tflops);
 

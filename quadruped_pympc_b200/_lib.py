@@ -69,7 +69,7 @@ EXPORTS = [
     'qpmpc_destroy', 'qpmpc_num_parameters', 'qpmpc_num_local_samples', 'qpmpc_tick', 'qpmpc_tick_iterations', 'qpmpc_step', 'qpmpc_step_flat', 'qpmpc_step_reset',
     'qpmpc_step_state', 'qpmpc_tick_batched',
     'qpmpc_tick_batched_flat',
-    'qpmpc_pgg_contact_sequence', 'qpmpc_footholds_reference', 'qpmpc_step_set_shift', 'qpmpc_kernel_name', 'qpmpc_shm_pack', 'qpmpc_publish_shm', 'qpmpc_stance_torques', 'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
+    'qpmpc_pgg_contact_sequence', 'qpmpc_footholds_reference', 'qpmpc_step_set_shift', 'qpmpc_kernel_name', 'qpmpc_debug_host_times', 'qpmpc_shm_pack', 'qpmpc_publish_shm', 'qpmpc_stance_torques', 'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
     'qpmpc_shard_peer_export', 'qpmpc_shard_peer_attach', 'qpmpc_shard_peer_loopback', 'qpmpc_shard_peer_inject',
@@ -148,6 +148,7 @@ def load():
                                             _FP, _FP, _FP, _FP, _FP, _IP, _FP]
     _DP = C.POINTER(C.c_double)
     lib.qpmpc_step_set_shift.argtypes = [H, C.c_float]
+    lib.qpmpc_debug_host_times.argtypes = [H, C.c_int32, C.POINTER(C.c_uint64)]
     lib.qpmpc_kernel_name.argtypes = [H]
     lib.qpmpc_kernel_name.restype = C.c_char_p
     lib.qpmpc_shm_pack.argtypes = [_DP, C.POINTER(C.c_uint64), _FP, _FP, _DP, _FP, C.c_double, C.c_double]

@@ -257,6 +257,8 @@ struct qpmpc_handle {
     bool helpers = false;             // tick_fn = tick_kernel_h (sample per thread + noise helper threads)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
     float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet + stamp (host / device alias)
+    bool host_times_on = false;                   // qpmpc_debug_host_times: CLOCK_MONOTONIC ns at entry / launched / stamp seen / unpacked
+    uint64_t host_ns[4] = {0, 0, 0, 0};
     float shift_step = 0.0f;                      // stateful controller: shift_solution step (1 / mpc_frequency), 0 = off
     mutable const float *last_out = nullptr;      // pinned host packets of the last unpacked tick (qpmpc_publish_shm)
     unsigned int seq = 0;
@@ -639,12 +641,20 @@ static inline unsigned int next_seq(qpmpc_handle *h) {
     if (++h->seq == 0) ++h->seq;                       // 0 is the initial content of every stamp
     return h->seq;
 }
+static inline uint64_t mono_ns() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
+}
 static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *out) {
+    const bool timed = h->host_times_on;
+    if (timed) h->host_ns[0] = mono_ns();
     memcpy(kp.packet, h->h_in, (size_t)kp.in_stride * sizeof(float));
     kp.param_packet = 1; kp.host_out = h->d_dout;
     if (kp.seq == 0) kp.seq = next_seq(h);
     int rc = launch(h, h->tick_fn, kp, grid);
     if (rc) return rc;
+    if (timed) h->host_ns[1] = mono_ns();
     volatile unsigned int *stamp = reinterpret_cast<volatile unsigned int *>(h->h_dout + kp.out_stride);
     for (unsigned long long spins = 1; *stamp != kp.seq; ++spins) {
         if ((spins & 0xffff) == 0) {             // a failed launch would never stamp: surface the error instead
@@ -654,7 +664,16 @@ static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *
         }
     }
     __sync_synchronize();
+    if (timed) h->host_ns[2] = mono_ns();
     unpack_one(h, 0, h->h_dout, &out[0]);
+    if (timed) h->host_ns[3] = mono_ns();
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_debug_host_times(qpmpc_handle *h, int32_t enable, uint64_t out[4]) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    h->host_times_on = enable != 0;
+    if (out) memcpy(out, h->host_ns, sizeof(h->host_ns));
     return QPMPC_OK;
 }
 

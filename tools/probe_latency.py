@@ -79,6 +79,20 @@ def e2e(method='mppi', param='cubic_spline', N=10000, lanes=0, io_mode='direct',
         lib.qpmpc_tick(h, C.byref(b.cin), C.byref(b.cout))
         clat.append((time.perf_counter_ns() - t0) * 1e-3)
     print(f'    bare qpmpc_tick: p50 {np.percentile(clat, 50):.1f} us  p99 {np.percentile(clat, 99):.1f} us')
+    if io_mode == 'direct':                # host-side timeline of the direct-I/O tick
+        ns = (C.c_uint64 * 4)()
+        lib.qpmpc_debug_host_times(h, 1, None)
+        seg = []
+        for i in range(ticks):
+            t0 = time.perf_counter_ns()
+            lib.qpmpc_tick(h, C.byref(b.cin), C.byref(b.cout))
+            t1 = time.perf_counter_ns()
+            lib.qpmpc_debug_host_times(h, 1, ns)
+            seg.append([ns[1] - ns[0], ns[2] - ns[1], ns[3] - ns[2], (t1 - t0) - (ns[3] - ns[0])])
+        lib.qpmpc_debug_host_times(h, 0, None)
+        m = np.median(np.array(seg, dtype=np.float64), axis=0) * 1e-3
+        print(f'    host timeline (median us): packet + cudaLaunchKernel {m[0]:.1f} | launch -> stamp seen {m[1]:.1f} | '
+              f'unpack {m[2]:.1f} | pack_one + ctypes {m[3]:.1f}')
     print(f'e2e N={N} lanes={lanes} io={io_mode} graph={use_graph}: p50 {np.percentile(lat, 50):.1f} us  p99 '
           f'{np.percentile(lat, 99):.1f} us  best_cost {float(out[4]):.3f}', flush=True)
 
