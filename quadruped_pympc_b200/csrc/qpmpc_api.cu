@@ -249,6 +249,9 @@ struct qpmpc_handle {
     size_t noise_capacity = 0, freqs_capacity = 0;
     cudaGraphExec_t graph_exec = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // chunk-pipelined batched tick (pipelined_batch): second compute stream, upload / download streams, per-chunk events
+    cudaStream_t stream2 = nullptr, stream_in = nullptr, stream_out = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_chunk[8] = {}, ev_in[8] = {}, ev_k[8] = {};
     uint64_t launches = 0;
     bool resident_uploaded = false, partial_done = false;
     NcclComm comm = nullptr;
@@ -356,6 +359,15 @@ static void free_handle(qpmpc_handle *h) {
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
     cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg); cudaFree(h->d_frg);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
+    if (h->stream_in) cudaStreamDestroy(h->stream_in);
+    if (h->stream_out) cudaStreamDestroy(h->stream_out);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    for (int c = 0; c < 8; ++c) {
+        if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
+        if (h->ev_in[c]) cudaEventDestroy(h->ev_in[c]);
+        if (h->ev_k[c]) cudaEventDestroy(h->ev_k[c]);
+    }
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     cudaFree(h->d_in); cudaFree(h->d_out); cudaFree(h->d_costs); cudaFree(h->d_blk); cudaFree(h->d_send); cudaFree(h->d_recv);
@@ -600,11 +612,11 @@ static int ensure_freqs(qpmpc_handle *h, size_t floats) {
     return QPMPC_OK;
 }
 
-static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid) {
+static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid, cudaStream_t stream = nullptr) {
     void *args[] = {(void *)&kp};
     const bool is_finish = (fn == h->finish_fn);
     CK(cudaLaunchKernel((const void *)fn, grid, dim3(is_finish ? TB : h->threads), args,
-                        is_finish ? h->finish_smem_bytes : h->smem_bytes, h->stream));
+                        is_finish ? h->finish_smem_bytes : h->smem_bytes, stream ? stream : h->stream));
     h->launches++;
     return QPMPC_OK;
 }
@@ -805,11 +817,130 @@ extern "C" int qpmpc_footholds_reference(qpmpc_handle *h, const double *base_pos
     return QPMPC_OK;
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Chunk-pipelined batched tick (host arrays in, host arrays out; R >= PIPE_MIN_ROBOTS).  The robots are independent, so
+// the batch is cut into up to 8 chunks: an upload stream copies chunk c+1 (packed on the host meanwhile) while chunk c
+// computes, a download stream returns chunk c-1 (unpacked on the host meanwhile), and the chunk kernels alternate
+// between two compute streams so that the tail wave of one chunk is filled by the next -- the copy engines and the host
+// work hide behind the kernels instead of bracketing one big launch.  Every per-robot array is addressed as
+// base + robot * stride in the kernels, so a chunk is the same kernel on offset base pointers (and robot_base, which
+// keeps the Philox streams).
+// ------------------------------------------------------------------------------------------------------
+static const int PIPE_MIN_ROBOTS = 64;
+
+static int validate_one(const qpmpc_handle *h, int r, const qpmpc_tick_in *in, uint32_t seed0, bool stateful) {
+    if (!in->state || !in->reference) return fail(QPMPC_ERR_INVALID, "state / reference must not be NULL");
+    if (!in->contact_sequence && !h->contacts_on_device) return fail(QPMPC_ERR_INVALID, "contact_sequence is NULL and no device-generated table is armed (qpmpc_pgg_contact_sequence)");
+    if (in->contact_sequence && in->contact_ld < h->H) return fail(QPMPC_ERR_INVALID, "contact_ld %d < horizon %d", in->contact_ld, h->H);
+    if (h->cfg.adaptive && !in->phase_signal) return fail(QPMPC_ERR_INVALID, "phase_signal is required by the gait-adaptive controller");
+    if (!stateful && in->key[0] != seed0) return fail(QPMPC_ERR_INVALID, "all robots of one batch must share key[0] (robot %d differs); streams differ by robot id", r);
+    if (!stateful && h->cfg.method == QPMPC_CEM_MPPI && !in->sigma) return fail(QPMPC_ERR_INVALID, "sigma is required by cem_mppi");
+    for (int l = 0; l < 4 && in->contact_sequence; ++l)
+        for (int n = 0; n < h->H; ++n) {
+            const float c = in->contact_sequence[(size_t)l * in->contact_ld + n];
+            if (c != 0.0f && c != 1.0f) return fail(QPMPC_ERR_INVALID, "contact_sequence[%d][%d] = %g is not 0 or 1", l, n, (double)c);
+        }
+    return QPMPC_OK;
+}
+
+static void offset_robots(KParams &kp, int r0) {
+    kp.in += (size_t)r0 * kp.in_stride; kp.out += (size_t)r0 * kp.out_stride;
+    kp.costs += (size_t)r0 * kp.n_local;
+    kp.blk_recs += (size_t)r0 * kp.nblk * kp.blk_rec_stride;
+    kp.shard_send += (size_t)r0 * kp.shard_rec_stride;
+    kp.counters += r0;
+    if (kp.cem_hist) kp.cem_hist += (size_t)r0 * CEM_BINS;
+    if (kp.contact_dev) kp.contact_dev += (size_t)r0 * 4 * kp.H;
+    if (kp.ctrl_state) kp.ctrl_state += (size_t)r0 * kp.ctrl_stride;
+    kp.robot_base += (uint32_t)r0;
+}
+
+static void shift_basis(const qpmpc_handle *h, KParams &kp);
+
+// stateful: qpmpc_step semantics (iterations launches per chunk, sigma reset / shift at iteration 0)
+static int pipelined_batch(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out, bool stateful, int iterations,
+                           float sigma0) {
+    const int R = h->R;
+    const bool timed = h->host_times_on;                   // qpmpc_debug_host_times: entered / all chunks issued / last chunk back / unpacked
+    if (timed) h->host_ns[0] = mono_ns();
+    for (int r = 0; r < R; ++r) { int rc = validate_one(h, r, &in[r], in[0].key[0], stateful); if (rc) return rc; }
+    if (!h->stream2) {
+        CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->stream_in, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->stream_out, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+        for (int c = 0; c < 8; ++c) {
+            CK(cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_in[c], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_k[c], cudaEventDisableTiming));
+        }
+    }
+    const int per = std::max(32, (R + 7) / 8), C = (R + per - 1) / per;
+    CK(cudaEventRecord(h->ev_fork, h->stream));            // after whatever the handle queued before (device tables, resets)
+    CK(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+    CK(cudaStreamWaitEvent(h->stream_in, h->ev_fork, 0));
+    auto pack_chunk = [&](int c) {
+        for (int r = c * per; r < std::min(R, (c + 1) * per); ++r) { int rc = pack_one(h, r, &in[r], false, stateful); if (rc) return rc; }
+        return (int)QPMPC_OK;
+    };
+    int rc = pack_chunk(0);                                 // (cannot fail after validate_one; sets kp.seed from robot 0)
+    if (rc) return rc;
+    if (stateful) h->kp.seed = h->cfg.seed;
+    KParams base = h->kp;
+    if (h->contacts_on_device && in[0].contact_sequence == nullptr) base.contact_dev = h->d_contact;   // bind_device_contacts,
+    base.in = h->d_in; base.out = h->d_out;                // (the armed flag is dropped after the last chunk is packed)
+    if (stateful) { base.ctrl_state = h->d_ctrl; base.ctrl_stride = h->ctrl_stride; base.sigma0 = sigma0; }
+    for (int c = 0; c < C && rc == QPMPC_OK; ++c) {
+        const int r0 = c * per, rn = std::min(per, R - r0);
+        cudaStream_t st = (c & 1) ? h->stream2 : h->stream;
+        KParams kc = base;
+        offset_robots(kc, r0);
+        const size_t in_off = (size_t)r0 * base.in_stride, out_off = (size_t)r0 * base.out_stride;
+        CK(cudaMemcpyAsync(h->d_in + in_off, h->h_in + in_off, (size_t)rn * base.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream_in));
+        CK(cudaEventRecord(h->ev_in[c], h->stream_in));
+        CK(cudaStreamWaitEvent(st, h->ev_in[c], 0));
+        for (int it = 0; it < iterations && rc == QPMPC_OK; ++it) {
+            if (stateful) {
+                kc.sigma_reset = (it == 0 && h->cfg.method == QPMPC_CEM_MPPI) ? 1 : 0;
+                kc.shift_kind = 0;
+                if (it == 0 && h->shift_step > 0.0f) shift_basis(h, kc);
+            }
+            rc = launch(h, h->tick_fn, kc, dim3(kc.nblk, rn), st);
+        }
+        if (rc == QPMPC_OK) {
+            CK(cudaEventRecord(h->ev_k[c], st));
+            CK(cudaStreamWaitEvent(h->stream_out, h->ev_k[c], 0));
+            CK(cudaMemcpyAsync(h->h_out + out_off, h->d_out + out_off, (size_t)rn * base.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream_out));
+            CK(cudaEventRecord(h->ev_chunk[c], h->stream_out));
+            if (c + 1 < C) rc = pack_chunk(c + 1);          // host packing of the next chunk overlaps this chunk's kernels
+        }
+    }
+    h->contacts_on_device = false;
+    if (rc != QPMPC_OK) {
+        cudaStreamSynchronize(h->stream_in); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->stream2); cudaStreamSynchronize(h->stream_out);
+        return rc;
+    }
+    if (timed) h->host_ns[1] = mono_ns();
+    for (int c = 0; c < C; ++c) {
+        CK(cudaEventSynchronize(h->ev_chunk[c]));
+        if (timed && c == C - 1) h->host_ns[2] = mono_ns();
+        for (int r = c * per; r < std::min(R, (c + 1) * per); ++r) unpack_one(h, r, h->h_out, &out[r]);
+    }
+    if (timed) h->host_ns[3] = mono_ns();
+    // every download waited for its chunk's kernels and those for their upload: all four streams are idle here
+    return QPMPC_OK;
+}
+
 static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out) {
     if (!h || !in || !out) return fail(QPMPC_ERR_INVALID, "NULL argument");
     if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "handle is a shard: use qpmpc_tick_sharded / qpmpc_shard_partial");
     CK(cudaSetDevice(h->cfg.device));
     const int R = h->R;
+    if (R >= PIPE_MIN_ROBOTS && h->cfg.io_mode != QPMPC_IO_MAPPED) {
+        bool injected = false;
+        for (int r = 0; r < R; ++r) injected |= (in[r].noise != nullptr || in[r].step_freqs != nullptr);
+        if (!injected) return pipelined_batch(h, in, out, false, 1, 0.0f);
+    }
     for (int r = 0; r < R; ++r) { int rc = pack_one(h, r, &in[r], false); if (rc) return rc; }
     KParams kp = h->kp;
     bind_device_contacts(h, in, kp);
@@ -979,8 +1110,10 @@ extern "C" int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iter
     if (rc) return rc;
     const int R = h->R;
     const uint32_t seed = h->cfg.seed;
-    for (int r = 0; r < R; ++r) {
+    for (int r = 0; r < R; ++r)
         if (in[r].noise || in[r].step_freqs) return fail(QPMPC_ERR_INVALID, "the stateful controller draws its own noise: use qpmpc_tick for injection");
+    if (R >= PIPE_MIN_ROBOTS && h->cfg.io_mode != QPMPC_IO_MAPPED) return pipelined_batch(h, in, out, true, iterations, sigma0);
+    for (int r = 0; r < R; ++r) {
         rc = pack_one(h, r, &in[r], false, true);
         if (rc) return rc;
     }

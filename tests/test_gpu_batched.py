@@ -182,3 +182,51 @@ def test_stance_torque_epilogue(built):
         F = o[0][3 * leg:3 * leg + 3].astype(np.float64) * float(sc['contact_sequence'][leg, 0])
         np.testing.assert_allclose(t1[3 * leg:3 * leg + 3], -np.matmul(jac[0, leg].astype(np.float64).T, F), rtol=1e-5, atol=1e-4)
         np.testing.assert_allclose(g1[3 * leg:3 * leg + 3], F, rtol=1e-7)
+
+
+@pytest.mark.parametrize('method,adaptive', [('mppi', False), ('cem_mppi', False), ('random_sampling', True)])
+@pytest.mark.parametrize('R', [64, 77, 300])
+def test_chunk_pipelined_batch_equals_small_batches(built, method, adaptive, R):
+    """R >= 64 robots with host arrays run as up to 8 chunks alternating between two streams (upload / kernels / download
+    overlapped).  The result must be bit-identical to the same robots run in small un-pipelined handles (same robot ids),
+    for ragged chunk sizes, stateless and stateful (2 iterations), and a failing robot must fail the call up front."""
+    N = 400
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='linear_spline',
+                                     num_parallel_computations=N, optimize_step_freq=adaptive, lanes_per_sample=1)
+    st, rf, cs, ph, _ = _scenarios('go2', R)
+    key = np.array([42, 17], np.uint32)
+    P = 36
+    rng = np.random.RandomState(1)
+    best0 = (0.2 * rng.randn(R, P)).astype(np.float32)
+    kw = dict(timing=ph, nominal_step_frequency=1.4, optimize_swing=1)
+    big = BatchedSampling_MPC(cfg, R)
+    whole = big.compute_control(st, rf, cs, best0, key=key, **kw)
+    parts = []
+    for lo in range(0, R, 29):                                  # 29 < 64: the un-pipelined path
+        hi = min(R, lo + 29)
+        b = BatchedSampling_MPC(cfg, hi - lo, robot_base=lo)
+        parts.append(b.compute_control(st[lo:hi], rf[lo:hi], cs[lo:hi], best0[lo:hi], key=key,
+                                       timing=ph[lo:hi], nominal_step_frequency=1.4, optimize_swing=1))
+    for i in range(len(whole)):
+        np.testing.assert_array_equal(whole[i], np.concatenate([p[i] for p in parts]))
+    np.testing.assert_array_equal(big.fetch_costs(R - 1), b.fetch_costs(R - 1 - lo))
+    # stateful, two ticks of two iterations
+    big2 = BatchedSampling_MPC(cfg, R)
+    smalls = [(lo, min(R, lo + 29)) for lo in range(0, R, 29)]
+    sm = [BatchedSampling_MPC(cfg, hi - lo, robot_base=lo) for lo, hi in smalls]
+    for tick in range(2):
+        st_t = st + 0.01 * tick
+        w = big2.step(st_t, rf, cs, iterations=2, **kw)
+        ps = [m.step(st_t[lo:hi], rf[lo:hi], cs[lo:hi], timing=ph[lo:hi], nominal_step_frequency=1.4, optimize_swing=1,
+                     iterations=2) for m, (lo, hi) in zip(sm, smalls)]
+        for i in range(len(w)):
+            np.testing.assert_array_equal(w[i], np.concatenate([p[i] for p in ps]))
+    # a bad contact table in the LAST chunk is refused before anything is launched: the carried state is untouched
+    bad = cs.copy()
+    bad[R - 1, 2, 3] = 0.5
+    with pytest.raises(Exception):
+        big2.step(st, rf, bad, iterations=1, **kw)
+    again = big2.step(st + 0.02, rf, cs, iterations=2, **kw)
+    ps = [m.step(st[lo:hi] + 0.02, rf[lo:hi], cs[lo:hi], timing=ph[lo:hi], nominal_step_frequency=1.4, optimize_swing=1,
+                 iterations=2) for m, (lo, hi) in zip(sm, smalls)]
+    np.testing.assert_array_equal(again[2], np.concatenate([p[2] for p in ps]))

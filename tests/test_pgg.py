@@ -42,13 +42,13 @@ def test_device_tables_reproduce_the_reference_gait_generator(built):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('R', [37, 90])          # 90: the chunk-pipelined batched path
 @pytest.mark.parametrize('method', ['mppi', 'cem_mppi'])
-def test_batched_tables_feed_the_tick_from_the_device(built, method):
+def test_batched_tables_feed_the_tick_from_the_device(built, method, R):
     import quadruped_pympc_b200 as qp
     from quadruped_pympc_b200 import synthetic
     from quadruped_pympc_b200.batched import BatchedSampling_MPC
     from quadruped_pympc_b200.gait import contact_sequences_from_phase, PHASE_OFFSETS
-    R = 37
     cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, num_parallel_computations=500, lanes_per_sample=1)
     a, b = BatchedSampling_MPC(cfg, R), BatchedSampling_MPC(cfg, R)
     rng = np.random.RandomState(3)

@@ -97,6 +97,34 @@ def e2e(method='mppi', param='cubic_spline', N=10000, lanes=0, io_mode='direct',
           f'{np.percentile(lat, 99):.1f} us  best_cost {float(out[4]):.3f}', flush=True)
 
 
+def batched_e2e(R=512, N=10000, ticks=30):
+    """host arrays in / out through BatchedSampling_MPC.compute_control, with the host-side timeline of the C call"""
+    from quadruped_pympc_b200.batched import BatchedSampling_MPC
+    cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', control_parametrization='cubic_spline', num_parallel_computations=N)
+    ctrl = BatchedSampling_MPC(cfg, R)
+    scs = [synthetic.scenario('go2', 'trot', seed=r) for r in range(R)]
+    st = np.stack([s['state'] for s in scs]).astype(np.float32)
+    rf = np.stack([s['reference'] for s in scs]).astype(np.float32)
+    cs = np.stack([s['contact_sequence'] for s in scs]).astype(np.float32)
+    best = np.zeros((R, ctrl.num_control_parameters), np.float32)
+    lib, h = _lib.load(), ctrl._ensure()
+    lib.qpmpc_debug_host_times(h, 1, None)
+    ns = (C.c_uint64 * 4)()
+    rows = []
+    for i in range(ticks + 3):
+        ctrl.with_newkey()
+        t0 = time.perf_counter_ns()
+        out = ctrl.compute_control(st, rf, cs, best)
+        t1 = time.perf_counter_ns()
+        best = out[2]
+        lib.qpmpc_debug_host_times(h, 1, ns)
+        if i >= 3:
+            rows.append([t1 - t0, ns[1] - ns[0], ns[2] - ns[1], ns[3] - ns[2], (t1 - t0) - (ns[3] - ns[0])])
+    m = np.median(np.array(rows, dtype=np.float64), axis=0) * 1e-3
+    print(f'batched e2e R={R} N={N}: call {m[0]:.0f} us = validate + pack + issue {m[1]:.0f} | wait for the last chunk {m[2]:.0f} | '
+          f'unpack of the last chunk {m[3]:.0f} | flat wrapper + python {m[4]:.0f}', flush=True)
+
+
 if __name__ == '__main__':
     what = sys.argv[1] if len(sys.argv) > 1 else 'quick'
     tf = C.c_float(0)
@@ -128,6 +156,8 @@ if __name__ == '__main__':
                 ms, _ = resident(N=10000, R=R, lanes=lanes, steps=10)
                 row.append(ms * 1e3)
             print(f'N=   10000  R={R:<4d} lanes1 {row[0]:9.1f} us   lanes4 {row[1]:9.1f} us', flush=True)
+    if what in ('quick', 'batched'):
+        batched_e2e()
     if what in ('quick', 'e2e'):
         for lanes in (1, 14, 4):
             e2e(lanes=lanes)
