@@ -147,3 +147,26 @@ def test_kernel_variants_agree_bit_for_bit_on_ragged_sizes(built, method, N):
     # four lanes: a different summation order inside the rollout -> FP32 tolerance of the north_star
     np.testing.assert_allclose(np.asarray(outs[2][6]), np.asarray(outs[0][6]), rtol=3 * COST_RTOL)
     np.testing.assert_allclose(np.asarray(outs[2][0]), np.asarray(outs[0][0]), rtol=1e-4, atol=1e-3)
+
+
+def test_kernel_variant_selection(built):
+    """lanes_per_sample = 0: four lanes per sample up to 6 144 samples per launch, sample per thread + noise helpers for one
+    controller of up to 148 tiles, plain sample per thread otherwise (batches, multi-tile launches)."""
+    import quadruped_pympc_b200 as qp
+    from quadruped_pympc_b200.batched import BatchedSampling_MPC
+
+    def name(N, lanes=0, robots=None):
+        cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=N, lanes_per_sample=lanes)
+        if robots is None:
+            return qp.Sampling_MPC(cfg).kernel_name
+        from quadruped_pympc_b200 import _lib
+        b = BatchedSampling_MPC(cfg, robots)
+        return _lib.load().qpmpc_kernel_name(b._ensure()).decode()
+
+    assert name(4000) == 'tick_kernel_quad'
+    assert name(10000) == 'tick_kernel_h'
+    assert name(148 * 128) == 'tick_kernel_h' and name(148 * 128 + 1) == 'tick_kernel'
+    assert name(10000, lanes=1) == 'tick_kernel' and name(10000, lanes=4) == 'tick_kernel_quad'
+    assert name(200000, lanes=14) == 'tick_kernel'                 # does not qualify: falls back
+    assert name(10000, robots=2) == 'tick_kernel' and name(10000, lanes=14, robots=2) == 'tick_kernel'
+    assert name(1000, robots=4) == 'tick_kernel_quad'
