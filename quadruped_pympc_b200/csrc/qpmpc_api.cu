@@ -259,7 +259,8 @@ struct qpmpc_handle {
     int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
     bool helpers = false;             // tick_fn = tick_kernel_h (sample per thread + noise helper threads)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
-    float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet + stamp (host / device alias)
+    float *h_dout = nullptr, *d_dout = nullptr;   // mapped pinned result packet as {value, seq} units (host / device alias)
+    float *h_dec = nullptr;                       // the same packet decoded to plain floats (direct_tick)
     bool host_times_on = false;                   // qpmpc_debug_host_times: CLOCK_MONOTONIC ns at entry / launched / stamp seen / unpacked
     uint64_t host_ns[4] = {0, 0, 0, 0};
     float shift_step = 0.0f;                      // stateful controller: shift_solution step (1 / mpc_frequency), 0 = off
@@ -376,6 +377,7 @@ static void free_handle(qpmpc_handle *h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->h_rec) cudaFreeHost(h->h_rec);
     if (h->h_dout) cudaFreeHost(h->h_dout);
+    free(h->h_dec);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -529,8 +531,10 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     kp.seed = cfg->seed; kp.robot_base = (uint32_t)cfg->robot_base;
     h->direct = (cfg->io_mode == QPMPC_IO_DIRECT && h->R == 1 && kp.in_stride <= PACKET_MAX);   // W > 1: peer-exchange ticks only
     if (h->direct) {
-        CKH(cudaHostAlloc((void **)&h->h_dout, (kp.out_stride + 4) * sizeof(float), cudaHostAllocMapped));
-        memset(h->h_dout, 0, (kp.out_stride + 4) * sizeof(float));
+        CKH(cudaHostAlloc((void **)&h->h_dout, (size_t)kp.out_stride * 2 * sizeof(float), cudaHostAllocMapped));
+        memset(h->h_dout, 0, (size_t)kp.out_stride * 2 * sizeof(float));      // flag 0 is never a valid seq (next_seq)
+        h->h_dec = (float *)calloc((size_t)kp.out_stride, sizeof(float));
+        if (!h->h_dec) { free_handle(h); return fail(QPMPC_ERR_INVALID, "out of host memory"); }
         CKH(cudaHostGetDevicePointer((void **)&h->d_dout, h->h_dout, 0));
     }
     *out = h;
@@ -667,17 +671,23 @@ static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *
     int rc = launch(h, h->tick_fn, kp, grid);
     if (rc) return rc;
     if (timed) h->host_ns[1] = mono_ns();
-    volatile unsigned int *stamp = reinterpret_cast<volatile unsigned int *>(h->h_dout + kp.out_stride);
-    for (unsigned long long spins = 1; *stamp != kp.seq; ++spins) {
-        if ((spins & 0xffff) == 0) {             // a failed launch would never stamp: surface the error instead
-            cudaError_t q = cudaStreamQuery(h->stream);
-            if (q != cudaSuccess && q != cudaErrorNotReady) return fail(QPMPC_ERR_CUDA, "tick kernel failed: %s", cudaGetErrorString(q));
-            if (q == cudaSuccess && *stamp != kp.seq) return fail(QPMPC_ERR_CUDA, "tick kernel finished without stamping its result");
+    // every 8-byte unit {value, seq} validates itself: take each one as soon as its flag is this tick's seq
+    const volatile uint64_t *unit = reinterpret_cast<const volatile uint64_t *>(h->h_dout);
+    uint32_t *dec = reinterpret_cast<uint32_t *>(h->h_dec);
+    unsigned long long spins = 0;
+    for (int u = 0; u < kp.out_stride; ++u) {
+        uint64_t w;
+        while ((uint32_t)((w = unit[u]) >> 32) != kp.seq) {
+            if ((++spins & 0xffff) == 0) {       // a failed launch would never publish: surface the error instead
+                cudaError_t q = cudaStreamQuery(h->stream);
+                if (q != cudaSuccess && q != cudaErrorNotReady) return fail(QPMPC_ERR_CUDA, "tick kernel failed: %s", cudaGetErrorString(q));
+                if (q == cudaSuccess && (uint32_t)(unit[u] >> 32) != kp.seq) return fail(QPMPC_ERR_CUDA, "tick kernel finished without publishing its result");
+            }
         }
+        dec[u] = (uint32_t)w;
     }
-    __sync_synchronize();
     if (timed) h->host_ns[2] = mono_ns();
-    unpack_one(h, 0, h->h_dout, &out[0]);
+    unpack_one(h, 0, h->h_dec, &out[0]);
     if (timed) h->host_ns[3] = mono_ns();
     return QPMPC_OK;
 }
@@ -1631,6 +1641,7 @@ extern "C" int qpmpc_debug_phase_times(qpmpc_handle *h, uint64_t out[16]) {
     CK(cudaMemsetAsync(h->d_phase, 0, 16 * sizeof(unsigned long long), h->stream));
     KParams kp = h->kp;
     kp.in = h->d_in; kp.out = h->d_out; kp.carry_best = 1; kp.phase_ns = h->d_phase;
+    if (h->direct) { kp.host_out = h->d_dout; kp.seq = next_seq(h); }     // include the direct-I/O result publication (slot 15 -> 11)
     int rc = launch(h, h->tick_fn, kp, dim3(kp.nblk, h->R));
     if (rc) return rc;
     CK(cudaMemcpyAsync(out, h->d_phase, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
