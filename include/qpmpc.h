@@ -48,8 +48,9 @@ typedef enum {
     QPMPC_IO_MEMCPY = 0,  /* pinned staging + cudaMemcpyAsync H2D / D2H around the kernel */
     QPMPC_IO_MAPPED = 1,  /* kernel reads/writes mapped pinned host memory directly (zero-copy over PCIe) */
     QPMPC_IO_DIRECT = 2   /* default for one controller: the tick packet travels in the kernel's parameter space, the last
-                             block stores the result packet + a completion stamp to mapped pinned host memory and the host
-                             spins on the stamp -- no copy-engine hop and no stream synchronisation around the kernel.
+                             block stores the result packet to mapped pinned host memory as self-validating 8-byte
+                             {value, tick sequence} units and the host takes each unit when its sequence matches -- no
+                             copy-engine hop, no system-scope fence and no stream synchronisation around the kernel.
                              Falls back to QPMPC_IO_MEMCPY for batched / sharded handles and oversized packets. */
 } qpmpc_io_mode;
 
