@@ -294,16 +294,19 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
         for (int p = t; p < kp.P; p += QTB) rec[REC_V + p] = s.v[p];
-    __threadfence();
+    // release / acquire around the ticket by ONE thread between two block barriers (the shape of cooperative groups'
+    // grid sync): the barrier orders the block's record stores before thread 0's fence, which is cumulative; the last
+    // block's readers are ordered after thread 0's second fence by the second barrier.  128 membars per block -> 1.
     __syncthreads();
     if (t == 0) {
+        __threadfence();
         const unsigned int ticket = atomicAdd(kp.counters + r, 1u);
         s_last = (ticket == (unsigned int)(kp.nblk - 1));
+        if (s_last) __threadfence();
     }
     __syncthreads();
     if (blk == 0) phase_mark(kp, 5);
     if (!s_last) return;
-    __threadfence();
     phase_mark(kp, 8);
     float M, S; int IDX;
     shard_reduce<METHOD, QTB>(kp, r, s, M, IDX, S);

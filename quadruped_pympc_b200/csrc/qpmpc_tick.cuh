@@ -558,8 +558,7 @@ __device__ bool peer_exchange(const KParams &kp, int r, const float *&recs, size
 template <int PARAM, bool ADAPTIVE, int METHOD, int NT>
 __device__ __forceinline__ void after_shard_reduce(const KParams &kp, int r, const Smem &s, float M, int IDX, float S) {
     if (kp.fused_finish) {
-        __threadfence();
-        __syncthreads();
+        __syncthreads();                               // the shard record (elite keys) is read back by this block only
         finish<PARAM, ADAPTIVE, METHOD, NT>(kp, r, s, kp.shard_send + (size_t)r * kp.shard_rec_stride, 1, 0, true, M, IDX, S);
         publish_to_host<NT>(kp, r);
     } else if (kp.peer_world > 1) {
@@ -682,16 +681,19 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
         for (int p = t; p < kp.P; p += TB) rec[REC_V + p] = s.v[p];
-    __threadfence();
+    // release / acquire around the ticket by ONE thread between two block barriers (the shape of cooperative groups'
+    // grid sync): the barrier orders the block's record stores before thread 0's fence, which is cumulative; the last
+    // block's readers are ordered after thread 0's second fence by the second barrier.  128 membars per block -> 1.
     __syncthreads();
     if (t == 0) {
+        __threadfence();
         const unsigned int ticket = atomicAdd(kp.counters + r, 1u);
         s_last = (ticket == (unsigned int)(kp.nblk - 1));
+        if (s_last) __threadfence();
     }
     __syncthreads();
     if (blk == 0) phase_mark(kp, 5);
     if (!s_last) return;
-    __threadfence();
     phase_mark(kp, 8);
     float M, S; int IDX;
     shard_reduce<METHOD, TB>(kp, r, s, M, IDX, S);
