@@ -93,6 +93,10 @@ class LazyCosts:
         return (self._owner._n_local,)
 
 
+_ZERO_FOOTHOLDS = np.zeros(12, dtype=np.int32)
+_ZERO_FOOTHOLDS.setflags(write=False)
+
+
 class _TickBuffers:
     """ctypes in/out structs bound ONCE to preallocated float32 staging arrays: a tick only copies values into them
     (no allocation, no pointer re-binding on the tick path).  Views onto the fixed-size members of the out struct let
@@ -113,6 +117,7 @@ class _TickBuffers:
         self._p_sigma, self._p_timing = _fp(self.sigma_in), _fp(self.timing)
         o.best, o.sigma_new = _fp(self.best_out), _fp(self.sigma_out)
         o.elite_indices = self.elite.ctypes.data_as(C.POINTER(C.c_int32))
+        self.key_view = np.ctypeslib.as_array(i.key)           # uint32[2] view of cin.key
         self.grfs_view = np.ctypeslib.as_array(o.grfs)
         self.pred_view = np.ctypeslib.as_array(o.predicted_state)
         self.keep = []
@@ -143,8 +148,11 @@ class _TickBuffers:
             i.phase_signal = None
         i.nominal_step_freq = float(nominal) if nominal is not None else 0.0
         i.optimize_swing = int(optimize_swing) if optimize_swing is not None else 0
-        k0, k1 = key.tolist() if isinstance(key, np.ndarray) else key
-        i.key[0], i.key[1] = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
+        if isinstance(key, np.ndarray) and key.dtype == np.uint32 and key.shape == (2,):
+            self.key_view[...] = key                            # the class's own master_key: one small copy
+        else:
+            k0, k1 = key.tolist() if isinstance(key, np.ndarray) else key
+            i.key[0], i.key[1] = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
         self.keep = [noise, step_freqs]                     # parity hooks only; already float32 C-contiguous
         i.noise, i.step_freqs = _fp(noise), _fp(step_freqs)
 
@@ -547,10 +555,11 @@ class Sampling_MPC:
         o = b.cout
         grfs = b.grfs_view.copy()
         pred = b.pred_view.copy()
-        footholds = np.zeros(12, dtype=np.int32)                    # S:748
+        footholds = _ZERO_FOOTHOLDS                                 # S:748 (read-only zeros; the interface ignores them, I:170-175)
         best = b.best_out.copy()
-        self.last_best_index = int(o.best_index)
-        res = (grfs, footholds, pred, best, np.float32(o.best_cost), float(np.float32(o.best_freq)), LazyCosts(self))
+        self.last_best_index = o.best_index
+        # best_freq: a c_float field reads back as the exact float32 value already
+        res = (grfs, footholds, pred, best, np.float32(o.best_cost), o.best_freq, LazyCosts(self))
         if self.sampling_method == 'cem_mppi':
             self.last_elite_indices = b.elite[:o.num_elite].astype(np.int64)
             res = res + (b.sigma_out.copy(),)
