@@ -214,6 +214,7 @@ struct NcclApi {
     int (*CommInitRank)(NcclComm *, int, NcclId, int) = nullptr;
     int (*AllGather)(const void *, void *, size_t, int, NcclComm, cudaStream_t) = nullptr;
     int (*CommDestroy)(NcclComm) = nullptr;
+    int (*CommAbort)(NcclComm) = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
 };
 static NcclApi g_nccl;
@@ -225,6 +226,7 @@ static int load_nccl(const char *path) {
     g_nccl.CommInitRank = (int (*)(NcclComm *, int, NcclId, int))dlsym(lib, "ncclCommInitRank");
     g_nccl.AllGather = (int (*)(const void *, void *, size_t, int, NcclComm, cudaStream_t))dlsym(lib, "ncclAllGather");
     g_nccl.CommDestroy = (int (*)(NcclComm))dlsym(lib, "ncclCommDestroy");
+    g_nccl.CommAbort = (int (*)(NcclComm))dlsym(lib, "ncclCommAbort");
     g_nccl.GetErrorString = (const char *(*)(int))dlsym(lib, "ncclGetErrorString");
     if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.CommDestroy)
         return fail(QPMPC_ERR_NCCL, "libnccl is missing required symbols");
@@ -355,7 +357,14 @@ extern "C" void qpmpc_config_defaults(qpmpc_config *c) {
 static void free_handle(qpmpc_handle *h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
-    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    if (h->comm) {
+        // Every tick is synchronous, so nothing is in flight on this communicator.  ncclCommAbort releases it locally;
+        // ncclCommDestroy's finalize step was seen to hang when NCCL-exchange handles are created and destroyed
+        // repeatedly in a process that also runs torch.distributed's own communicator (tools/multi_gpu_check.py).
+        if (h->stream) cudaStreamSynchronize(h->stream);
+        if (g_nccl.CommAbort) g_nccl.CommAbort(h->comm);
+        else if (g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    }
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
     cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg); cudaFree(h->d_frg);

@@ -41,6 +41,7 @@ def main():
     ap.add_argument('--out', default='')
     ap.add_argument('--sizes', default='1000,10000,100000,1000000')
     ap.add_argument('--exchange', default='peer,nccl')
+    ap.add_argument('--first-case', type=int, default=0, help='skip the cases before this index')
     args = ap.parse_args()
     rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
     torch.cuda.set_device(local)
@@ -53,7 +54,7 @@ def main():
               ('go2', 'trot', 'cem_mppi', 'linear_spline', False, 10000)]
     t_start = time.perf_counter()
     for exchange in args.exchange.split(','):
-        for robot, gait, method, param, adaptive, N in cases:
+        for robot, gait, method, param, adaptive, N in cases[args.first_case:]:
             cfg = qp.SamplerConfig.for_robot(robot, sampling_method=method, control_parametrization=param,
                                              num_parallel_computations=N, optimize_step_freq=adaptive, device=local)
             ctrl = make_sharded_controller(cfg, exchange=exchange)
@@ -107,7 +108,7 @@ def main():
                         'elapsed_s': round(time.perf_counter() - t_start, 1)}
                 print(json.dumps(line), flush=True)
                 lines.append(line)
-            del ctrl
+            del ctrl                     # (NCCL-exchange handles release their communicator with ncclCommAbort)
             dist.barrier()
     if rank == 0 and args.out:
         with open(args.out, 'w') as f:
