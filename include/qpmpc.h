@@ -146,7 +146,11 @@ int qpmpc_tick_iterations(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iter
  * footholds, knots of a leg that just lifted off zeroed, centroidal_nmpc_jax.py:563-627), then `iterations` sampling
  * iterations (with_newkey / best / with_newsigma carried; cem_mppi restarts from `sigma0` at iteration 0 like
  * srbd_controller_interface.py:128-129), then previous_contact <- contact_sequence[:, 0].  `out` = last iteration.
- * shift_solution is not supported here (config.py:194 default off). */
+ * shift_solution: see qpmpc_step_set_shift.
+ * Error behaviour: invalid inputs are rejected before anything is launched (no robot advances).  A CUDA error in the
+ * middle of a chunk-pipelined batch (R >= 64) drains all streams and returns QPMPC_ERR_CUDA; the device records of the
+ * chunks already launched HAVE advanced, so the caller must qpmpc_step_reset before stepping again (the error string
+ * says so). */
 int qpmpc_step(qpmpc_handle *h, const qpmpc_tick_in *in, int32_t iterations, float sigma0, qpmpc_tick_out *out);
 /* shift_solution (mpc_params['shift_solution'], config.py:194) for the stateful controller: step > 0 makes every
  * qpmpc_step* first write the carried best's spline value at `step` (= 1 / mpc_frequency, S:571-573) into knots [0], [2],

@@ -5,17 +5,24 @@ TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is product code: only
 ``--impl reference`` legs may import it, and only as the checker or the timed CPU
 baseline.  The product path (``quadruped_pympc_b200``) never imports this module.
 
-PARITY UNPINNED: the reference ships no golden vectors / known-answer tests for
-this path and its implementation needs ``jax``/``jaxlib``
-(pinned 0.9.2 in the reference's pixi.lock), ``gym_quadruped`` and ``mujoco``,
-none of which exist in this image (no network).  This file is therefore an
-op-for-op NumPy restatement of the reference's Python, vectorised over the
-sample axis, with every function citing the reference file:line it follows
-(paths relative to /root/reference/quadruped_pympc/).  It is pinned only by
-(i) a float64 twin of itself, (ii) an independent statement of the same SRBD
-equations (controllers/gradient/nominal/centroidal_model_nominal.py:201-272,
-restated in tests/test_oracle.py with numpy.linalg), (iii) analytic properties
-and (iv) the C twin in oracle/sampling_oracle.c.
+PARITY PINNED by the reference's own source: ``tools/make_golden.py`` executes the
+reference's UNMODIFIED controllers/sampling/*.py, centroidal_model_jax.py,
+helpers/periodic_gait_generator_jax.py and config.py from /root/reference under a
+NumPy stand-in for the ~40 jax entry points they use (``oracle/jaxshim``; jax/jaxlib
+0.9.2, gym_quadruped and mujoco are not installable in this image -- no network) and
+freezes 22 tick fixtures + host-side fixtures under ``tests/golden/``.  This file and
+its C twin reproduce every fixture (costs rel 2e-6, argmin exact, knots/GRFs/sigma
+1e-5; tests/test_golden.py).  What the fixtures pin: formulas, indexing, op order and
+control flow of the reference as written.  What they cannot pin: XLA's own fusion /
+re-association (covered by the north_star's float32 tolerance) and threefry bit
+streams (noise is injected, as the north_star prescribes).
+This file is an op-for-op NumPy restatement of the reference's Python, vectorised
+over the sample axis, with every function citing the reference file:line it follows
+(paths relative to /root/reference/quadruped_pympc/).  Further cross-checks: (i) a
+float64 twin of itself, (ii) an independent statement of the same SRBD equations
+(controllers/gradient/nominal/centroidal_model_nominal.py:201-272, restated in
+tests/test_oracle.py with numpy.linalg), (iii) analytic properties and (iv) the C
+twin in oracle/sampling_oracle.c.
 
 Conventions
 -----------

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstring>
 #include <ctime>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -191,16 +192,17 @@ __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
 // kernel dispatch tables (parametrisation x adaptive x method)
 // ------------------------------------------------------------------------------------------------------
 static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3];
-static void fill_kernel_tables() {
-    static bool done = false;
-    if (done) return;
+static void fill_kernel_tables_once() {
     qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER], g_tick_h_table[ZERO_ORDER]);
     qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR], g_tick_h_table[LINEAR]);
     qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC], g_tick_h_table[CUBIC]);
     qp_inst_quad_zero(g_quad_table[ZERO_ORDER]);
     qp_inst_quad_linear(g_quad_table[LINEAR]);
     qp_inst_quad_cubic(g_quad_table[CUBIC]);
-    done = true;
+}
+static void fill_kernel_tables() {             // handles may be created concurrently (ROS2 thread mode)
+    static std::once_flag once;
+    std::call_once(once, fill_kernel_tables_once);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -315,6 +317,9 @@ static int validate_config(const qpmpc_config *c) {
         return fail(QPMPC_ERR_INVALID, "num_splines must be in [1,%d]", QPMPC_MAX_SPLINES);
     if (c->num_robots < 1) return fail(QPMPC_ERR_INVALID, "num_robots must be >= 1");
     if (c->robot_base < 0) return fail(QPMPC_ERR_INVALID, "robot_base must be >= 0");
+    // the global robot id shares Philox counter word 0 with the quad index (bits 0-7) and the stream flag (bit 8)
+    if ((long long)c->robot_base + c->num_robots > (1ll << 23))
+        return fail(QPMPC_ERR_INVALID, "robot_base + num_robots = %lld exceeds 2^23 (robot id field of the Philox counter)", (long long)c->robot_base + c->num_robots);
     if (c->shard_world < 1 || c->shard_rank < 0 || c->shard_rank >= c->shard_world) return fail(QPMPC_ERR_INVALID, "bad shard rank/world");
     if (!(c->mass > 0.f)) return fail(QPMPC_ERR_INVALID, "mass must be positive");
     if (c->elite_k < 0 || c->elite_k > QPMPC_MAX_ELITE) return fail(QPMPC_ERR_INVALID, "elite_k must be in [0,%d]", QPMPC_MAX_ELITE);
@@ -572,10 +577,12 @@ static int pack_one(qpmpc_handle *h, int r, const qpmpc_tick_in *in, bool explic
     if (h->cfg.adaptive && !in->phase_signal) return fail(QPMPC_ERR_INVALID, "phase_signal is required by the gait-adaptive controller");
     rec[IN_NOMFREQ] = in->nominal_step_freq;
     rec[IN_OPTSWING] = u2f((uint32_t)in->optimize_swing);
+    // Philox counter word 3 (the seed) travels in the packet and is read from there by the kernels: a graph-captured
+    // launch freezes kernel-parameter space at capture time, the packet is uploaded every tick.
     if (stateful) { /* keys are ignored: the record holds the counter, the seed is the handle's */ }
-    else if (r == 0) h->kp.seed = in->key[0];             // Philox key word 0 travels in kernel-parameter space (block-uniform)
+    else if (r == 0) h->kp.seed = in->key[0];
     else if (in->key[0] != h->kp.seed) return fail(QPMPC_ERR_INVALID, "all robots of one batch must share key[0] (robot %d differs); streams differ by robot id", r);
-    rec[IN_SEED] = u2f(in->key[0]);
+    rec[IN_SEED] = u2f(stateful ? h->cfg.seed : in->key[0]);
     rec[IN_TICK] = u2f(in->key[1]);
     rec[IN_ROBOT] = u2f((uint32_t)(h->cfg.robot_base + r));   // global robot id = Philox key word 1
     for (int l = 0; l < 4 && in->contact_sequence; ++l)
@@ -671,6 +678,14 @@ static inline uint64_t mono_ns() {
     clock_gettime(CLOCK_MONOTONIC, &ts);
     return (uint64_t)ts.tv_sec * 1000000000ull + (uint64_t)ts.tv_nsec;
 }
+// The {value, seq} units rely on the GPU's 16-byte PCIe stores arriving as atomic aligned 8-byte halves and on the host
+// reading an aligned uint64_t with one load: true on x86-64 and on AArch64 (both guarantee single-copy atomicity of
+// naturally aligned 8-byte accesses); any other host must use QPMPC_IO_MEMCPY.
+#if !defined(__x86_64__) && !defined(__aarch64__)
+#error "direct_tick: the {value, seq} publication needs single-copy-atomic aligned 8-byte loads on the host"
+#endif
+static_assert(sizeof(uint64_t) == 8 && alignof(uint64_t) == 8, "8-byte units");
+static const uint64_t DIRECT_TICK_DEADLINE_NS = 4000000000ull;   // > the in-kernel peer wait (2 s), so that one reports first
 static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *out) {
     const bool timed = h->host_times_on;
     if (timed) h->host_ns[0] = mono_ns();
@@ -684,6 +699,7 @@ static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *
     const volatile uint64_t *unit = reinterpret_cast<const volatile uint64_t *>(h->h_dout);
     uint32_t *dec = reinterpret_cast<uint32_t *>(h->h_dec);
     unsigned long long spins = 0;
+    uint64_t t_spin0 = 0;
     for (int u = 0; u < kp.out_stride; ++u) {
         uint64_t w;
         while ((uint32_t)((w = unit[u]) >> 32) != kp.seq) {
@@ -691,6 +707,11 @@ static int direct_tick(qpmpc_handle *h, KParams &kp, dim3 grid, qpmpc_tick_out *
                 cudaError_t q = cudaStreamQuery(h->stream);
                 if (q != cudaSuccess && q != cudaErrorNotReady) return fail(QPMPC_ERR_CUDA, "tick kernel failed: %s", cudaGetErrorString(q));
                 if (q == cudaSuccess && (uint32_t)(unit[u] >> 32) != kp.seq) return fail(QPMPC_ERR_CUDA, "tick kernel finished without publishing its result");
+                // a hung kernel (or a peer wait that never ends) must not block a real-time loop for ever
+                const uint64_t now = mono_ns();
+                if (t_spin0 == 0) t_spin0 = now;
+                else if (now - t_spin0 > DIRECT_TICK_DEADLINE_NS)
+                    return fail(QPMPC_ERR_CUDA, "tick kernel did not publish its result within %.1f s", 1e-9 * (double)DIRECT_TICK_DEADLINE_NS);
             }
         }
         dec[u] = (uint32_t)w;
@@ -915,9 +936,12 @@ static int pipelined_batch(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_
         KParams kc = base;
         offset_robots(kc, r0);
         const size_t in_off = (size_t)r0 * base.in_stride, out_off = (size_t)r0 * base.out_stride;
-        CK(cudaMemcpyAsync(h->d_in + in_off, h->h_in + in_off, (size_t)rn * base.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream_in));
-        CK(cudaEventRecord(h->ev_in[c], h->stream_in));
-        CK(cudaStreamWaitEvent(st, h->ev_in[c], 0));
+        // CKL: a CUDA error inside the loop must not return with work in flight on four streams -- record it, leave the
+        // loop and drain through the common path below
+#define CKL(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess && rc == QPMPC_OK) rc = fail(QPMPC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+        CKL(cudaMemcpyAsync(h->d_in + in_off, h->h_in + in_off, (size_t)rn * base.in_stride * sizeof(float), cudaMemcpyHostToDevice, h->stream_in));
+        CKL(cudaEventRecord(h->ev_in[c], h->stream_in));
+        CKL(cudaStreamWaitEvent(st, h->ev_in[c], 0));
         for (int it = 0; it < iterations && rc == QPMPC_OK; ++it) {
             if (stateful) {
                 kc.sigma_reset = (it == 0 && h->cfg.method == QPMPC_CEM_MPPI) ? 1 : 0;
@@ -927,16 +951,23 @@ static int pipelined_batch(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_
             rc = launch(h, h->tick_fn, kc, dim3(kc.nblk, rn), st);
         }
         if (rc == QPMPC_OK) {
-            CK(cudaEventRecord(h->ev_k[c], st));
-            CK(cudaStreamWaitEvent(h->stream_out, h->ev_k[c], 0));
-            CK(cudaMemcpyAsync(h->h_out + out_off, h->d_out + out_off, (size_t)rn * base.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream_out));
-            CK(cudaEventRecord(h->ev_chunk[c], h->stream_out));
-            if (c + 1 < C) rc = pack_chunk(c + 1);          // host packing of the next chunk overlaps this chunk's kernels
+            CKL(cudaEventRecord(h->ev_k[c], st));
+            CKL(cudaStreamWaitEvent(h->stream_out, h->ev_k[c], 0));
+            CKL(cudaMemcpyAsync(h->h_out + out_off, h->d_out + out_off, (size_t)rn * base.out_stride * sizeof(float), cudaMemcpyDeviceToHost, h->stream_out));
+            CKL(cudaEventRecord(h->ev_chunk[c], h->stream_out));
+            if (rc == QPMPC_OK && c + 1 < C) rc = pack_chunk(c + 1);   // host packing of the next chunk overlaps this chunk's kernels
         }
+#undef CKL
     }
     h->contacts_on_device = false;
     if (rc != QPMPC_OK) {
+        // drain every stream; in stateful mode the chunks already launched have advanced their device records (best,
+        // key counter, previous contact) while this call fails: the batch is half-advanced and the caller must
+        // qpmpc_step_reset before the next step (documented in include/qpmpc.h)
         cudaStreamSynchronize(h->stream_in); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->stream2); cudaStreamSynchronize(h->stream_out);
+        const std::string first = g_err;
+        (void)cudaGetLastError();
+        g_err = first + (stateful ? " [stateful batch half-advanced: call qpmpc_step_reset]" : "");
         return rc;
     }
     if (timed) h->host_ns[1] = mono_ns();
@@ -1042,7 +1073,10 @@ static int ensure_ctrl(qpmpc_handle *h) {
         rec[2 * h->P] = u2f(1u);                       // master_key counter after the first with_newkey()
         rec[2 * h->P + 1] = u2f(0xFu);                 // previous_contact_mpc = [1, 1, 1, 1], I:19
     }
-    CK(cudaMemcpy(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    // on the handle's (non-blocking) stream: ordered behind a tick whose tail may still be running (direct_tick returns
+    // as soon as the stamped packet is on the host)
+    CK(cudaMemcpyAsync(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     h->kp.seed = h->cfg.seed;
     return QPMPC_OK;
 }
@@ -1062,7 +1096,8 @@ extern "C" int qpmpc_step_reset(qpmpc_handle *h, const uint32_t key[2], const fl
         if (previous_contact) { m = 0u; for (int l = 0; l < 4; ++l) m |= (previous_contact[4 * r + l] != 0 ? 1u : 0u) << l; }
         rec[2 * h->P + 1] = u2f(m);
     }
-    CK(cudaMemcpy(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpyAsync(h->d_ctrl, init.data(), n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     h->kp.seed = key[0];
     h->cfg.seed = key[0];
     return QPMPC_OK;
@@ -1074,7 +1109,8 @@ extern "C" int qpmpc_step_state(qpmpc_handle *h, int robot, float *best, float *
     int rc = ensure_ctrl(h);
     if (rc) return rc;
     std::vector<float> rec((size_t)h->ctrl_stride);
-    CK(cudaMemcpy(rec.data(), h->d_ctrl + (size_t)robot * h->ctrl_stride, rec.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpyAsync(rec.data(), h->d_ctrl + (size_t)robot * h->ctrl_stride, rec.size() * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     if (best) memcpy(best, rec.data(), (size_t)h->P * sizeof(float));
     if (sigma) memcpy(sigma, rec.data() + h->P, (size_t)h->P * sizeof(float));
     if (previous_contact) { const uint32_t m = f2u(rec[2 * h->P + 1]); for (int l = 0; l < 4; ++l) previous_contact[l] = (m >> l) & 1u; }

@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     if (blk == 0) phase_mark(kp, 0);
     stage_inputs<QTB>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
-    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
+    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + slot;
     const float *tleg = tcol + leg * kp.P_leg * QTS;

@@ -6,6 +6,7 @@
 namespace qp {
 
 constexpr int MAXV = 6;                 // P <= MAXV * TB knots
+static_assert(MAXV * TB / 4 <= 256, "the quad index must fit bits 0-7 of Philox counter word 0 (qpmpc_kernels.cuh noise_quad_nz)");
 constexpr int SCRATCH_KEYS = 2048;      // u64 keys for the cross-shard elite merge (world * elite_k <= 2048)
 constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogram + misc
 
@@ -300,7 +301,9 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     // premerged: the caller (fused single-shard tick) has just produced (M, IDX, S, s.v) in shard_reduce
     if (!premerged) merge_records<METHOD, NT>(recs, world, rec_stride, kp.P, s, M, IDX, S);
     float *out = kp.out + (size_t)r * kp.out_stride;
-    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
+    // the seed is read from the staged packet (IN_SEED), never from kernel-parameter space: a CUDA-graph-captured launch
+    // freezes its parameters at capture time, the packet is uploaded every tick
+    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_best = s.in + kp.off_best;
     const float *s_sigma = s.in + kp.off_sigma;
     // ---- new best into s.v ----
@@ -592,7 +595,7 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     if (blk == 0) phase_mark(kp, 0);
     stage_inputs<TB * NH>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
-    const uint32_t seed = kp.seed, robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
+    const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
     const float *s_sigma = s.in + kp.off_sigma;
     float *tcol = s.tile + t;
     float m_run = CUDART_INF_F, s_run = 0.0f;

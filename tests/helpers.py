@@ -80,6 +80,28 @@ def knot_atol(ref_costs, got_costs, weights, noise, floor=2e-4):
     return floor + 2.0 * dc * amp
 
 
+PARITY_LOG = []       # one record per checked vector: (name, max |err| / (rtol |x| + ulp), fell_back, excess) -- dumped by conftest
+
+
+def _assert_knots(name, got, ref, atol_fallback):
+    """north_star first: |got - ref| <= 1e-4 |ref| + one float32 ulp of the largest entry.  Only if that fails, the
+    softmax-amplification bound `knot_atol` (docstring above) is allowed, and the excess over the plain tolerance is
+    recorded and printed."""
+    g, r = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+    ulp = float(np.spacing(np.float32(np.max(np.abs(r))))) if r.size else 0.0
+    tol = KNOT_RTOL * np.abs(r) + ulp
+    err = np.abs(g - r)
+    ratio = float(np.max(err / tol)) if r.size else 0.0
+    if ratio <= 1.0:
+        PARITY_LOG.append((name, ratio, False, 0.0))
+        return
+    excess = float(np.max(err - tol))
+    PARITY_LOG.append((name, ratio, True, excess))
+    print(f'[parity] {name}: plain north_star tolerance (rtol 1e-4 + 1 ulp = {ulp:.2e}) exceeded by {excess:.3e} '
+          f'(x{ratio:.2f}); falling back to the softmax-amplification bound atol = {atol_fallback:.3e}')
+    np.testing.assert_allclose(got, ref, rtol=KNOT_RTOL, atol=atol_fallback)
+
+
 def assert_tick_parity(ref, got, cem=False, noise=None):
     rel = np.max(np.abs(got['costs'] - ref['costs']) / np.maximum(np.abs(ref['costs']), 1e-12))
     assert rel < COST_RTOL, f'cost rel err {rel:.3e} >= {COST_RTOL}'
@@ -87,8 +109,8 @@ def assert_tick_parity(ref, got, cem=False, noise=None):
     np.testing.assert_allclose(got['best_cost'], ref['best_cost'], rtol=COST_RTOL)
     noise = got.get('_noise') if noise is None else noise
     atol = knot_atol(ref['costs'], got['costs'], ref.get('weights'), noise)
-    np.testing.assert_allclose(got['best_control_parameters'], ref['best_control_parameters'], rtol=KNOT_RTOL, atol=atol)
-    np.testing.assert_allclose(got['nmpc_GRFs'], ref['nmpc_GRFs'], rtol=KNOT_RTOL, atol=atol)
+    _assert_knots('knots', got['best_control_parameters'], ref['best_control_parameters'], atol)
+    _assert_knots('GRFs', got['nmpc_GRFs'], ref['nmpc_GRFs'], atol)
     np.testing.assert_allclose(got['nmpc_predicted_state'], ref['nmpc_predicted_state'], rtol=KNOT_RTOL, atol=1e-6)
     np.testing.assert_allclose(got['best_freq'], ref['best_freq'], rtol=1e-6)
     if cem:

@@ -110,3 +110,14 @@ def test_from_reference_config_module():
         'shift_solution': False, 'device': 'gpu'})
     cfg = qp.SamplerConfig.from_reference(mod)
     assert cfg.sampling_method == 'mppi' and cfg.num_control_parameters == 36 and cfg.mass == 24.637
+
+
+def test_robot_ids_must_fit_the_philox_counter_field(built):
+    """The global robot id is bits 9..31 of Philox counter word 0: robot_base + num_robots > 2^23 would alias another
+    robot's noise stream, so qpmpc_create rejects it (before it needs a device)."""
+    lib = _lib.load()
+    c = make_c_config(qp.SamplerConfig.for_robot('go2'), num_robots=4)
+    c.robot_base = (1 << 23) - 3
+    h = C.c_void_p()
+    assert lib.qpmpc_create(C.byref(c), C.byref(h)) == _lib.ERR_INVALID
+    assert b'2^23' in lib.qpmpc_last_error()

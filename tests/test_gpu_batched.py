@@ -230,3 +230,28 @@ def test_chunk_pipelined_batch_equals_small_batches(built, method, adaptive, R):
     ps = [m.step(st[lo:hi] + 0.02, rf[lo:hi], cs[lo:hi], timing=ph[lo:hi], nominal_step_frequency=1.4, optimize_swing=1,
                  iterations=2) for m, (lo, hi) in zip(sm, smalls)]
     np.testing.assert_array_equal(again[2], np.concatenate([p[2] for p in ps]))
+
+
+@pytest.mark.parametrize('R,io_mode', [(2, 'direct'), (5, 'direct'), (1, 'memcpy')])
+def test_graph_captured_tick_follows_a_changed_seed(built, R, io_mode):
+    """Batches of 2 <= R < 64 and io_mode='memcpy' replay a CUDA graph captured on the first tick.  The Philox seed
+    (key[0]) must not be frozen with it: a handle that ticks with key (42, 1) and then (43, 1) must return, for the
+    second tick, what a fresh handle returns for (43, 1), and the tick must equal the oracle on generate_noise(key)."""
+    N = 700
+    kw = dict(sampling_method='mppi', control_parametrization='cubic_spline', num_parallel_computations=N, io_mode=io_mode)
+    cfg = qp.SamplerConfig.for_robot('go2', **kw)
+    st, rf, cs, ph, scs = _scenarios('go2', R)
+    best0 = np.zeros((R, cfg.num_control_parameters), np.float32)
+    used = BatchedSampling_MPC(cfg, R)
+    first = used.compute_control(st, rf, cs, best0, key=np.array([42, 1], np.uint32))
+    again = used.compute_control(st, rf, cs, best0, key=np.array([43, 1], np.uint32))
+    fresh = BatchedSampling_MPC(cfg, R).compute_control(st, rf, cs, best0, key=np.array([43, 1], np.uint32))
+    assert not np.array_equal(first[2], again[2])
+    for a, b in zip(again, fresh):
+        np.testing.assert_array_equal(a, b)
+    orc = SamplingOracle(OracleConfig.for_robot('go2', **{k: v for k, v in kw.items() if k != 'io_mode'}))
+    for r in range(R):
+        noise = used.generate_noise(r, key=np.array([43, 1], np.uint32))
+        ref = orc.compute_control(scs[r]['state'], scs[r]['reference'], scs[r]['contact_sequence'], best0[r], noise)
+        assert again[5][r] == ref['best_index']
+        np.testing.assert_allclose(again[3][r], ref['best_cost'], rtol=1e-5)

@@ -170,3 +170,88 @@ def test_kernel_variant_selection(built):
     assert name(200000, lanes=14) == 'tick_kernel'                 # does not qualify: falls back
     assert name(10000, robots=2) == 'tick_kernel' and name(10000, lanes=14, robots=2) == 'tick_kernel'
     assert name(1000, robots=4) == 'tick_kernel_quad'
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Row a15: the device's own step-frequency sampler (csrc/qpmpc_kernels.cuh sample_step_freq) against the oracle.
+#   random_sampling A:687-691: choice(where(optimize_swing, step_freq_delta, nominal))
+#   mppi            A:835-838: choice(step_freq_delta), optimize_swing ignored
+#   cem_mppi        A:994-1000: choice([0, 0.2, 0.4]) * optimize_swing + nominal
+#   best_step_frequency = step_frequencies_vec[best_index]   A:705 | 861 | 1022
+# The choice indices come from the integer-exact host mirror of the Philox stream (oracle/sampling_oracle.c
+# orc_freq_choice), the assembly per method from the oracle (assemble_step_frequencies).
+# ------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('nominal', [1.4, 1.1])
+@pytest.mark.parametrize('optimize_swing', [0, 1])
+@pytest.mark.parametrize('method', METHODS)
+def test_device_step_freqs_match_oracle(built, method, optimize_swing, nominal):
+    from oracle import c_oracle
+    N = 5000
+    oracle, ctrl, ocfg = make_pair('go2', N, control_parametrization='linear_spline', sampling_method=method,
+                                   optimize_step_freq=True)
+    mirror = c_oracle.COracle(ocfg)
+    for key in ([42, 1], [42, 977], [7, 3]):
+        dev = ctrl.generate_step_freqs(np.array(key, np.uint32), nominal, optimize_swing)
+        choice = mirror.freq_choice(key[0], key[1])
+        assert choice.min() == 0 and choice.max() == 2 and np.all(np.bincount(choice, minlength=3) > N // 4)
+        want = oracle.assemble_step_frequencies(choice, nominal, optimize_swing)
+        np.testing.assert_array_equal(dev, want)
+        assert dev.dtype == np.float32 and want.dtype == np.float32
+
+
+def _production_adaptive_tick(oracle, ctrl, sc, method, optimize_swing, sigma=None, best0=None):
+    """One tick in production mode (in-kernel noise AND in-kernel step frequencies: nothing injected) and the oracle fed
+    with the tensors the device exports for the same key."""
+    ctrl.with_newkey()
+    key = ctrl.master_key.copy()
+    nominal = sc['nominal_step_freq']
+    noise = ctrl.generate_noise(key, sigma)
+    freqs = ctrl.generate_step_freqs(key, nominal, optimize_swing)
+    best0 = np.zeros(oracle.P, np.float32) if best0 is None else best0
+    ref = oracle.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, noise, sigma=sigma,
+                                 timing=sc['phase_signal'], nominal_step_frequency=nominal,
+                                 optimize_swing=optimize_swing, step_frequencies=freqs)
+    args = ((sigma,) if method == 'cem_mppi' else ()) + (sc['phase_signal'], nominal, optimize_swing)
+    out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *args)
+    got = dict(nmpc_GRFs=out[0], nmpc_predicted_state=out[2], best_control_parameters=out[3], best_cost=out[4],
+               best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
+    if method == 'cem_mppi':
+        got['new_sigma_cem_mppi'], got['elite_indices'] = out[7], ctrl.last_elite_indices
+    return ref, got, noise, freqs
+
+
+@pytest.mark.parametrize('lanes', LANES)
+@pytest.mark.parametrize('optimize_swing', [0, 1])
+@pytest.mark.parametrize('method', METHODS)
+def test_production_adaptive_tick_matches_oracle_on_exported_noise_and_freqs(built, method, optimize_swing, lanes):
+    """a15 end to end: gait-adaptive tick with NOTHING injected vs the oracle on the exported noise and frequencies;
+    best_freq = step_frequencies[best_index], best_index and the elite indices must match exactly."""
+    from oracle import c_oracle
+    N = 3000
+    for param in ('cubic_spline', 'zero_order'):
+        oracle, ctrl, ocfg = make_pair('go2', N, control_parametrization=param, sampling_method=method,
+                                       optimize_step_freq=True, lanes_per_sample=lanes)
+        sc = synthetic.scenario('go2', 'trot', seed=9)
+        sigma = np.linspace(0.5, 4.0, oracle.P).astype(np.float32) if method == 'cem_mppi' else None
+        for _ in range(2):                                   # two ticks: the key counter advances, the streams change
+            ref, got, noise, freqs = _production_adaptive_tick(oracle, ctrl, sc, method, optimize_swing, sigma)
+            # the exported frequencies are the oracle's own assembly of the mirrored Philox choices
+            choice = c_oracle.COracle(ocfg).freq_choice(int(ctrl.master_key[0]), int(ctrl.master_key[1]))
+            np.testing.assert_array_equal(freqs, oracle.assemble_step_frequencies(choice, sc['nominal_step_freq'], optimize_swing))
+            assert_tick_parity(ref, got, cem=(method == 'cem_mppi'), noise=noise)
+            assert got['best_freq'] == freqs[ref['best_index']]
+
+
+@pytest.mark.parametrize('lanes', LANES)
+def test_config3_full_size_production_mode(built, lanes):
+    """BASELINE config 3 as it runs in production: HyQReal pace, CEM-MPPI with step-frequency adaptation, cubic,
+    N = 50,000, 200 elites, in-kernel noise and in-kernel step frequencies."""
+    oracle, ctrl, _ = make_pair('hyqreal1', 50000, control_parametrization='cubic_spline', sampling_method='cem_mppi',
+                                optimize_step_freq=True, lanes_per_sample=lanes)
+    sc = synthetic.scenario('hyqreal1', 'pace', seed=3)
+    sigma = np.full(oracle.P, 3.0, np.float32)
+    ref, got, noise, freqs = _production_adaptive_tick(oracle, ctrl, sc, 'cem_mppi', 1, sigma)
+    assert len(got['elite_indices']) == 200
+    assert set(np.unique(freqs)) == {np.float32(1.4), np.float32(1.4) + np.float32(0.2), np.float32(1.4) + np.float32(0.4)}
+    assert_tick_parity(ref, got, cem=True, noise=noise)
+    assert got['best_freq'] == freqs[ref['best_index']]

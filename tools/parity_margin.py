@@ -1,21 +1,47 @@
-"""How far inside the north_star tolerances the CUDA tick sits: cost / knot error statistics vs the oracle."""
+"""How far inside the north_star tolerances the CUDA tick sits, per BASELINE config and kernel variant.
+
+For every case: sample-cost relative error (tolerance 1e-5), and for the returned knots / GRFs the worst
+|err| / (1e-4 |x| + 1 float32 ulp of the largest entry)  -- <= 1 means the PLAIN north_star tolerance holds; > 1 is where
+the MPPI softmax amplifies cost rounding (w = exp(-(c - c_min)) maps an absolute cost error 1:1 to a relative weight
+error; at cost ~ 800 one ulp is 6e-5) and tests/helpers.knot_atol is needed.  Run on the GPU box:
+    python tools/parity_margin.py > gpurun_out/parity_margin.log
+"""
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'tests'))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
 import numpy as np
 from quadruped_pympc_b200 import synthetic
-from helpers import make_pair, seeded_noise, seeded_freqs, run_both
+from helpers import make_pair, seeded_noise, seeded_freqs, run_both, knot_atol, KNOT_RTOL
 
-for method, param, adaptive in [('mppi', 'cubic_spline', False), ('random_sampling', 'zero_order', False),
-                                ('mppi', 'linear_spline', False), ('cem_mppi', 'cubic_spline', True)]:
-    for lanes in (1, 4):
-        worst_c, med_c, worst_k, worst_g, exact = 0, [], 0, 0, 0
-        for seed in range(6):
-            oracle, ctrl, _ = make_pair('go2', 10000, control_parametrization=param, sampling_method=method,
+CASES = [   # name, robot, gait, method, param, adaptive, N
+    ('config0 aliengo/trot/random_sampling/zero_order', 'aliengo', 'trot', 'random_sampling', 'zero_order', False, 10000),
+    ('config1 go2/trot/mppi/cubic', 'go2', 'trot', 'mppi', 'cubic_spline', False, 10000),
+    ('config2 hyqreal/pace/cem_mppi/cubic/adaptive', 'hyqreal1', 'pace', 'cem_mppi', 'cubic_spline', True, 50000),
+    ('go2/trot/mppi/linear', 'go2', 'trot', 'mppi', 'linear_spline', False, 10000),
+    ('go2/pace/mppi/zero_order/adaptive', 'go2', 'pace', 'mppi', 'zero_order', True, 10000),
+    ('go2/trot/cem_mppi/cubic', 'go2', 'trot', 'cem_mppi', 'cubic_spline', False, 10000),
+]
+SEEDS = range(6)
+
+
+def ratio(got, ref):
+    g, r = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+    tol = KNOT_RTOL * np.abs(r) + float(np.spacing(np.float32(np.max(np.abs(r)))))
+    return float(np.max(np.abs(g - r) / tol)), float(np.max(np.abs(g - r)))
+
+
+print('columns: cost rel err max / median / share bit-equal | knots: worst |err|/(1e-4|x|+ulp), abs err | GRFs: same | '
+      'ticks needing the softmax-amplification fallback (and the bound it was held to)')
+for name, robot, gait, method, param, adaptive, N in CASES:
+    for lanes in (1, 14, 4):
+        worst_c, med_c, exact, rk, ak, rg, ag, fb, fb_bound = 0.0, [], 0.0, 0.0, 0.0, 0.0, 0.0, 0, 0.0
+        for seed in SEEDS:
+            oracle, ctrl, _ = make_pair(robot, N, control_parametrization=param, sampling_method=method,
                                         optimize_step_freq=adaptive, lanes_per_sample=lanes)
-            sc = synthetic.scenario('go2', 'trot', seed=seed)
+            sc = synthetic.scenario(robot, gait, seed=seed)
             rng = np.random.RandomState(seed)
             best0 = (0.5 * rng.randn(oracle.P)).astype(np.float32)
             sigma = np.full(oracle.P, 3.0, np.float32) if method == 'cem_mppi' else None
@@ -23,9 +49,17 @@ for method, param, adaptive in [('mppi', 'cubic_spline', False), ('random_sampli
             freqs = seeded_freqs(oracle, seed) if adaptive else None
             ref, got = run_both(oracle, ctrl, sc, best0, noise, sigma=sigma, freqs=freqs)
             rel = np.abs(got['costs'] - ref['costs']) / np.abs(ref['costs'])
-            worst_c = max(worst_c, rel.max()); med_c.append(np.median(rel)); exact += np.mean(rel == 0)
-            worst_k = max(worst_k, np.abs(got['best_control_parameters'] - ref['best_control_parameters']).max())
-            worst_g = max(worst_g, np.abs(got['nmpc_GRFs'] - ref['nmpc_GRFs']).max())
+            worst_c = max(worst_c, float(rel.max())); med_c.append(float(np.median(rel))); exact += float(np.mean(rel == 0))
+            r1, a1 = ratio(got['best_control_parameters'], ref['best_control_parameters'])
+            r2, a2 = ratio(got['nmpc_GRFs'], ref['nmpc_GRFs'])
+            rk, ak, rg, ag = max(rk, r1), max(ak, a1), max(rg, r2), max(ag, a2)
+            if max(r1, r2) > 1.0:
+                fb += 1
+                fb_bound = max(fb_bound, knot_atol(ref['costs'], got['costs'], ref.get('weights'), noise))
             assert got['best_index'] == ref['best_index']
-        print(f'{method:16s} {param:13s} adaptive={int(adaptive)} lanes={lanes}: cost rel err max {worst_c:.2e} median '
-              f'{np.mean(med_c):.2e} bit-equal {exact / 6:.1%} | knots abs max {worst_k:.2e} | GRF abs max {worst_g:.2e}', flush=True)
+            if method == 'cem_mppi':
+                assert np.array_equal(got['elite_indices'], ref['elite_indices'])
+            ctrl.close()
+        print(f'{name:48s} lanes={lanes:2d}: cost {worst_c:.2e} / {np.mean(med_c):.2e} / {exact / len(SEEDS):5.1%} | '
+              f'knots {rk:6.3f}x, {ak:.2e} | GRFs {rg:6.3f}x, {ag:.2e} | fallback {fb}/{len(SEEDS)}'
+              + (f' (atol {fb_bound:.2e})' if fb else ''), flush=True)
