@@ -193,7 +193,7 @@ def _sampler_cfg(device):
                                       num_parallel_computations=N_SAMPLES, device=device)
 
 
-def make_resident_handle(device, robots, robot_base, n_samples=None):
+def make_resident_handle(device, robots, robot_base, n_samples=None, lanes=None):
     """A handle with `robots` controllers whose tick packets are uploaded once and stay in HBM."""
     from quadruped_pympc_b200 import _lib, synthetic
     from quadruped_pympc_b200.sampling_mpc import make_c_config
@@ -201,6 +201,8 @@ def make_resident_handle(device, robots, robot_base, n_samples=None):
     scfg = _sampler_cfg(device)
     if n_samples is not None:
         scfg.num_parallel_computations = int(n_samples)
+    if lanes is not None:
+        scfg.lanes_per_sample = int(lanes)
     c = make_c_config(scfg, robots)
     c.robot_base = robot_base
     h = C.c_void_p()

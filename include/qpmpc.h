@@ -85,7 +85,10 @@ typedef struct qpmpc_config {
     int32_t lanes_per_sample;     /* kernel variant: 1 = one sample per thread (throughput), 4 = four lanes per sample, one
                                      leg each (latency: one small controller), 14 = one sample per thread plus three
                                      noise-helper threads per sample (latency: one controller of up to 148 x 128 samples;
-                                     falls back to 1 when the launch does not qualify), 0 = choose by samples per launch */
+                                     falls back to 1 when the launch does not qualify), 2 = two samples per thread in
+                                     packed FP32 (FFMA2; throughput: batches and large sample counts, fixed gait only;
+                                     falls back to 1 for gait-adaptive controllers or when two of its 256-sample tiles do
+                                     not fit one SM), 0 = choose by samples per launch */
 } qpmpc_config;
 
 /* One robot's inputs for one tick = the arguments of jitted_compute_control (I:140-168) */

@@ -61,7 +61,7 @@ class SamplerConfig:
     io_mode: str = 'direct'          # 'direct' (packet in kernel params, result stamped into mapped host memory) | 'memcpy' | 'mapped'
     use_graph: bool = True
     elite_k: int = 0                 # 0 = reference default (10 / 200)
-    lanes_per_sample: int = 0        # kernel variant: 0 = auto, 1 = sample per thread, 4 = four lanes per sample, 14 = 1 + noise helpers
+    lanes_per_sample: int = 0        # kernel variant: 0 = auto, 1 = sample per thread, 2 = two samples per thread (packed FP32), 4 = four lanes per sample, 14 = 1 + noise helpers
     q_diag: Sequence[float] = Q_DIAG_DEFAULT
 
     def __post_init__(self):

@@ -3,6 +3,7 @@
 #include "../../include/qpmpc.h"
 #include "qpmpc_inst.cuh"
 #include "qpmpc_quad.cuh"
+#include "qpmpc_x2.cuh"
 
 #include <dlfcn.h>
 #include <unistd.h>
@@ -22,6 +23,9 @@ using namespace qp;
 // samples per launch (all robots) up to which the four-lanes-per-sample kernel is chosen automatically (measured
 // crossover on B200)
 static const long long QPMPC_QUAD_MAX_SAMPLES = 6144;    // r1g sweep: 4k -> quad 22.6 vs 24.1 us, 10k -> 26.7 vs 24.6 us
+// samples per launch (all robots) from which the two-samples-per-thread packed-FP32 kernel (qpmpc_x2.cuh) is chosen
+// automatically for fixed-gait controllers: one full wave of its 256-sample tiles on 148 SMs x 2 resident blocks
+static const long long QPMPC_X2_MIN_SAMPLES = 148ll * 2 * XS;
 
 // ------------------------------------------------------------------------------------------------------
 // error plumbing
@@ -191,7 +195,7 @@ __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
 // ------------------------------------------------------------------------------------------------------
 // kernel dispatch tables (parametrisation x adaptive x method)
 // ------------------------------------------------------------------------------------------------------
-static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3];
+static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3], g_x2_table[3][3];
 static void fill_kernel_tables_once() {
     qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER], g_tick_h_table[ZERO_ORDER]);
     qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR], g_tick_h_table[LINEAR]);
@@ -199,6 +203,9 @@ static void fill_kernel_tables_once() {
     qp_inst_quad_zero(g_quad_table[ZERO_ORDER]);
     qp_inst_quad_linear(g_quad_table[LINEAR]);
     qp_inst_quad_cubic(g_quad_table[CUBIC]);
+    qp_inst_x2_zero(g_x2_table[ZERO_ORDER]);
+    qp_inst_x2_linear(g_x2_table[LINEAR]);
+    qp_inst_x2_cubic(g_x2_table[CUBIC]);
 }
 static void fill_kernel_tables() {             // handles may be created concurrently (ROS2 thread mode)
     static std::once_flag once;
@@ -398,10 +405,11 @@ static void free_handle(qpmpc_handle *h) {
 
 extern "C" void qpmpc_destroy(qpmpc_handle *h) { free_handle(h); }
 
+static int samples_per_tile(int lanes) { return lanes == 4 ? QS : (lanes == 2 ? XS : TB); }
 static void plan_blocks(int n_local, int lanes, int *iters, int *nblk) {
-    const int per_tile = lanes == 4 ? QS : TB;         // samples per tile
+    const int per_tile = samples_per_tile(lanes);      // samples per tile
     const int tiles = (n_local + per_tile - 1) / per_tile;
-    const int cap = 148 * 4 * 2;                       // two full waves of resident CTAs on 148 SMs
+    const int cap = lanes == 2 ? 148 * 2 * 2 : 148 * 4 * 2;   // two full waves of resident CTAs on 148 SMs
     int it = (tiles + cap - 1) / cap;
     if (it < 1) it = 1;
     *iters = it;
@@ -448,8 +456,16 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     // controller at 10k samples), the sample-per-thread kernel executes ~1.8x fewer instructions per sample and wins
     // once its warps fill the machine.  lanes_per_sample = 0 picks by the number of samples of one launch.
     const int lps = cfg->lanes_per_sample;
-    if (lps != 0 && lps != 1 && lps != 4 && lps != 14) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1, 4 or 14"); }
+    if (lps != 0 && lps != 1 && lps != 2 && lps != 4 && lps != 14) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1, 2, 4 or 14"); }
     h->lanes = lps == 4 ? 4 : (lps != 0 ? 1 : ((long long)h->n_local * h->R <= QPMPC_QUAD_MAX_SAMPLES ? 4 : 1));
+    // two samples per thread in packed FP32 (tick_kernel_x2): fixed gait only, and only while two 256-sample tiles fit one
+    // SM (otherwise the plain kernel keeps more warps resident).  lanes_per_sample = 2 asks for it, 0 picks it once a
+    // launch fills the machine with such tiles; requests that do not qualify fall back to the sample-per-thread kernel.
+    {
+        const size_t x2_in_stride = round4((size_t)IN_CONTACT + 4 * H + 2 * (size_t)h->P);
+        const bool x2_ok = !cfg->adaptive && smem_floats((int)x2_in_stride, h->P, XS, XTS) * sizeof(float) <= 113 * 1024;
+        if (x2_ok && (lps == 2 || (lps == 0 && (long long)h->n_local * h->R >= QPMPC_X2_MIN_SAMPLES))) h->lanes = 2;
+    }
     plan_blocks(h->n_local, h->lanes, &kp.iters, &kp.nblk);
     // sample per thread + noise helper threads (tick_kernel_h): one controller, one tile per block, no more blocks than SMs
     h->helpers = (h->lanes == 1 && lps != 1 && h->R == 1 && kp.iters == 1 && kp.nblk <= 148);
@@ -494,16 +510,19 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
             kp.basis[n][0] = 1.0f - q; kp.basis[n][1] = q;
         }
     }
-    h->threads = h->lanes == 4 ? QTB : (h->helpers ? TB * NOISE_HELPERS : TB);
+    h->threads = h->lanes == 4 ? QTB : (h->lanes == 2 ? XTB : (h->helpers ? TB * NOISE_HELPERS : TB));
     h->finish_smem_bytes = smem_floats(kp.in_stride, h->P) * sizeof(float);
     if (h->lanes == 4)      // the CEM elite refit of finish() stages up to `threads` noise rows in the tile
         h->smem_bytes = smem_floats(kp.in_stride, h->P, QTB, cfg->method == QPMPC_CEM_MPPI ? QTB + 1 : QTS) * sizeof(float);
+    else if (h->lanes == 2)
+        h->smem_bytes = smem_floats(kp.in_stride, h->P, XS, XTS) * sizeof(float);
     else
         h->smem_bytes = h->finish_smem_bytes;
     if (h->smem_bytes > 227 * 1024) { delete h; return fail(QPMPC_ERR_INVALID, "tile of %d knots needs %zu B shared memory (> 227 KB)", h->P, h->smem_bytes); }
 
     fill_kernel_tables();
-    h->tick_fn = (h->lanes == 4 ? g_quad_table : (h->helpers ? g_tick_h_table : g_tick_table))[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    h->tick_fn = h->lanes == 2 ? g_x2_table[cfg->parametrization][cfg->method]
+                               : (h->lanes == 4 ? g_quad_table : (h->helpers ? g_tick_h_table : g_tick_table))[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
@@ -521,7 +540,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_in, R * kp.in_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_out, R * kp.out_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_costs, R * (size_t)h->N * sizeof(float)));
-    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + (h->lanes == 4 ? QS : TB) - 1) / (h->lanes == 4 ? QS : TB))) * kp.blk_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + samples_per_tile(h->lanes) - 1) / samples_per_tile(h->lanes))) * kp.blk_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_send, R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_recv, (size_t)W * R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
@@ -1143,7 +1162,7 @@ static void shift_basis(const qpmpc_handle *h, KParams &kp) {
 
 extern "C" const char *qpmpc_kernel_name(const qpmpc_handle *h) {
     if (!h) return "";
-    return h->lanes == 4 ? "tick_kernel_quad" : (h->helpers ? "tick_kernel_h" : "tick_kernel");
+    return h->lanes == 4 ? "tick_kernel_quad" : (h->lanes == 2 ? "tick_kernel_x2" : (h->helpers ? "tick_kernel_h" : "tick_kernel"));
 }
 
 extern "C" int qpmpc_step_set_shift(qpmpc_handle *h, float step) {

@@ -15,9 +15,15 @@ void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::Ker
 void qp_inst_quad_zero(qp::KernelFn quad[2][3]);
 void qp_inst_quad_linear(qp::KernelFn quad[2][3]);
 void qp_inst_quad_cubic(qp::KernelFn quad[2][3]);
+void qp_inst_x2_zero(qp::KernelFn x2[3]);
+void qp_inst_x2_linear(qp::KernelFn x2[3]);
+void qp_inst_x2_cubic(qp::KernelFn x2[3]);
 }
 
 #define QP_FILL(T, K, P)                                                                        \
     T[0][0] = qp::K<P, false, qp::RANDOM_SAMPLING>; T[0][1] = qp::K<P, false, qp::MPPI>;        \
     T[0][2] = qp::K<P, false, qp::CEM_MPPI>; T[1][0] = qp::K<P, true, qp::RANDOM_SAMPLING>;     \
     T[1][1] = qp::K<P, true, qp::MPPI>; T[1][2] = qp::K<P, true, qp::CEM_MPPI>;
+#define QP_FILL_X2(T, P)                                                                       \
+    T[0] = qp::tick_kernel_x2<P, qp::RANDOM_SAMPLING>; T[1] = qp::tick_kernel_x2<P, qp::MPPI>;     \
+    T[2] = qp::tick_kernel_x2<P, qp::CEM_MPPI>;

@@ -11,6 +11,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "qpmpc_math.cuh"
 
 namespace qp {
 
@@ -236,146 +237,132 @@ __device__ __forceinline__ float sample_step_freq(const KParams &kp, const float
 }
 
 // ======================================================================================================
-// SRBD: M:93-174 (fd + explicit Euler) and the cost S:450-451, one step, state in registers
+// SRBD: M:93-174 (fd + explicit Euler) and the cost S:450-451, one step, state in registers.
+// Written once for T = float (one sample per thread) and T = float2 (two samples per thread, packed FP32):
+// see qpmpc_math.cuh -- explicit round-to-nearest operations only, so both lane types give the same bits.
 // ======================================================================================================
-struct Body { float px, py, pz, vx, vy, vz, roll, pitch, yaw, wx, wy, wz; };
-
-// sin and cos of a roll / pitch angle.  |x| <= pi/4 (every sane rollout): the same minimax polynomials sincosf evaluates
-// after its range reduction, without the reduction and quadrant logic (~11 instructions instead of ~35, same <= 1 ulp
-// accuracy); larger angles (diverged samples) take the library path.
-__device__ __forceinline__ void sincos_small(float x, float *sn, float *cs) {
-    if (fabsf(x) <= 0.78539816f) {
-        const float x2 = x * x;
-        float ps = fmaf(x2, -1.9515295891e-4f, 8.3321608736e-3f);
-        ps = fmaf(ps, x2, -1.6666654611e-1f);
-        *sn = fmaf(x * x2, ps, x);
-        float pc = fmaf(x2, 2.443315711809948e-5f, -1.388731625493765e-3f);
-        pc = fmaf(pc, x2, 4.166664568298827e-2f);
-        pc = fmaf(pc, x2, -0.5f);
-        *cs = fmaf(pc, x2, 1.0f);
-    } else {
-        sincosf(x, sn, cs);
-    }
-}
+template <class T> struct BodyT { T px, py, pz, vx, vy, vz, roll, pitch, yaw, wx, wy, wz; };
+typedef BodyT<float> Body;
 
 // S:270-314 (box friction pyramid, same comparison order).  where(x > lo, x, lo) == fmaxf(x, lo) and where(x < hi, x, hi)
 // == fminf(x, hi) for every input the reference can produce, NaN included (a NaN force takes the bound, as `where`
 // does; only the sign of a zero can differ, which no later product can see): one FMNMX instead of FSETP + FSEL.
-__device__ __forceinline__ void clamp_leg(const KParams &kp, float &fx, float &fy, float &fz) {
-    fz = fminf(fmaxf(fz, kp.fz_min), kp.fz_max);
-    const float hi = kp.mu * fz, lo = -hi;
-    fx = fminf(fmaxf(fx, lo), hi);
-    fy = fminf(fmaxf(fy, lo), hi);
+template <class T>
+__device__ __forceinline__ void clamp_leg(const KParams &kp, T &fx, T &fy, T &fz) {
+    fz = qmin(qmax(fz, kp.fz_min), kp.fz_max);
+    const T hi = qmul(fz, kp.mu), lo = qneg(hi);
+    fx = qmin(qmax(fx, lo), hi);
+    fy = qmin(qmax(fy, lo), hi);
 }
 
 // Fx..: sum of stance forces; tx..: sum of (foot - com) x F (world frame), M:111-118,132-135
-// Yaw is unweighted and unbounded, but every sample of a tick starts from the same yaw0: sin/cos(yaw0) are computed once
-// per block (s_yaw = {yaw0, sin yaw0, cos yaw0}, stage_inputs) and each step only needs the small-angle polynomials of
-// the drift d = yaw - yaw0 plus the angle-addition identities (~16 instructions instead of sincosf's ~35, <= 2 ulp).
-__device__ __forceinline__ void sincos_yaw(float yaw, const float *s_yaw, float *sn, float *cs) {
-    const float d = yaw - s_yaw[0];
-    if (fabsf(d) <= 0.78539816f) {
-        float sd, cd;
-        sincos_small(d, &sd, &cd);
-        const float s0 = s_yaw[1], c0 = s_yaw[2];
-        *sn = fmaf(s0, cd, c0 * sd);
-        *cs = fmaf(c0, cd, -(s0 * sd));
-    } else {
-        sincosf(yaw, sn, cs);
-    }
+template <class T>
+__device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, const float *foot, T fx, T fy, T fz,
+                                        T &Fx, T &Fy, T &Fz, T &tx, T &ty, T &tz) {
+    const T rx = qsub(foot[0], b.px), ry = qsub(foot[1], b.py), rz = qsub(foot[2], b.pz);
+    Fx = qadd(Fx, fx); Fy = qadd(Fy, fy); Fz = qadd(Fz, fz);
+    tx = qadd(tx, qfms(ry, fz, qmul(rz, fy)));
+    ty = qadd(ty, qfms(rz, fx, qmul(rx, fz)));
+    tz = qadd(tz, qfms(rx, fy, qmul(ry, fx)));
 }
 
-__device__ __forceinline__ float srbd_step(const KParams &kp, Body &b, float Fx, float Fy, float Fz, float tx, float ty,
-                                           float tz, float dt, const float *ref, const float *s_yaw) {
-    const float ax = kp.inv_m * Fx, ay = kp.inv_m * Fy, az = fmaf(kp.inv_m, Fz, -9.81f);       // M:118
-    float sr, cr, sp, cp, sy, cy;
+// one term of e^T Q e on the state after the step, S:450-451.  Zero weights (x, y, yaw with the reference's Q) are
+// skipped by a block-uniform branch: (e * 0) * e adds exactly nothing for every finite e.
+template <class T>
+__device__ __forceinline__ void cost_term(T &c, T x, float ref, float q) {
+    if (q != 0.0f) { const T e = qsub(x, ref); c = qfma(qmul(e, q), e, c); }
+}
+
+template <class T>
+__device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T Fy, T Fz, T tx, T ty, T tz, float dt,
+                                       const float *ref, const float *s_yaw) {
+    const T ax = qmul(Fx, kp.inv_m), ay = qmul(Fy, kp.inv_m), az = qfma(Fz, kp.inv_m, -9.81f);       // M:118
+    T sr, cr, sp, cp, sy, cy;
     sincos_small(b.roll, &sr, &cr);
     sincos_small(b.pitch, &sp, &cp);
     sincos_yaw(b.yaw, s_yaw, &sy, &cy);
     // inverse of the conjugate Euler-rate matrix by cofactors with its structural zeros dropped, M:124-130,137
-    const float det = (cp * cr) * cr + sr * (cp * sr);
-    float rd;                                             // 1 / det on the SFU (<= 1 ulp; det = cos(pitch) is O(1))
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rd) : "f"(det));
-    const float e01 = (sr * sp) * rd, e02 = (cr * sp) * rd, e11 = (cp * cr) * rd, e12 = -(cp * sr) * rd;
-    const float e21 = sr * rd, e22 = cr * rd;
-    const float droll = b.wx + e01 * b.wy + e02 * b.wz;
-    const float dpitch = e11 * b.wy + e12 * b.wz;
-    const float dyaw = e21 * b.wy + e22 * b.wz;
+    const T cpcr = qmul(cp, cr), cpsr = qmul(cp, sr), srsp = qmul(sr, sp), crsp = qmul(cr, sp);
+    const T det = qfma(sr, cpsr, qmul(cpcr, cr));
+    const T rd = rcp_approx(det);                        // 1 / det on the SFU (<= 1 ulp; det = cos(pitch) is O(1))
+    const T e01 = qmul(srsp, rd), e02 = qmul(crsp, rd), e11 = qmul(cpcr, rd), e12 = qmul(qneg(cpsr), rd);
+    const T e21 = qmul(sr, rd), e22 = qmul(cr, rd);
+    const T droll = qfma(e02, b.wz, qfma(e01, b.wy, b.wx));
+    const T dpitch = qfma(e12, b.wz, qmul(e11, b.wy));
+    const T dyaw = qfma(e22, b.wz, qmul(e21, b.wy));
     // b_R_w (ZYX), M:141-155, applied to the world torque
-    const float r00 = cp * cy, r01 = cp * sy, r02 = -sp;
-    const float r10 = sr * sp * cy - cr * sy, r11 = sr * sp * sy + cr * cy, r12 = sr * cp;
-    const float r20 = cr * sp * cy + sr * sy, r21 = cr * sp * sy - sr * cy, r22 = cr * cp;
-    const float bx = r00 * tx + r01 * ty + r02 * tz;
-    const float by = r10 * tx + r11 * ty + r12 * tz;
-    const float bz = r20 * tx + r21 * ty + r22 * tz;
+    const T r00 = qmul(cp, cy), r01 = qmul(cp, sy);                                   // r02 = -sp
+    const T r10 = qfms(srsp, cy, qmul(cr, sy)), r11 = qfma(srsp, sy, qmul(cr, cy));   // r12 = sr cp
+    const T r20 = qfma(crsp, cy, qmul(sr, sy)), r21 = qfms(crsp, sy, qmul(sr, cy));   // r22 = cr cp
+    const T bx = qfnma(sp, tz, qfma(r01, ty, qmul(r00, tx)));
+    const T by = qfma(cpsr, tz, qfma(r11, ty, qmul(r10, tx)));
+    const T bz = qfma(cpcr, tz, qfma(r21, ty, qmul(r20, tx)));
     // angular acceleration Iinv * (b_R_w tau - w x (I w)), M:157-159
-    const float Iwx = kp.I[0] * b.wx + kp.I[1] * b.wy + kp.I[2] * b.wz;
-    const float Iwy = kp.I[3] * b.wx + kp.I[4] * b.wy + kp.I[5] * b.wz;
-    const float Iwz = kp.I[6] * b.wx + kp.I[7] * b.wy + kp.I[8] * b.wz;
-    const float hx = bx - (b.wy * Iwz - b.wz * Iwy);
-    const float hy = by - (b.wz * Iwx - b.wx * Iwz);
-    const float hz = bz - (b.wx * Iwy - b.wy * Iwx);
-    const float dwx = kp.Iinv[0] * hx + kp.Iinv[1] * hy + kp.Iinv[2] * hz;
-    const float dwy = kp.Iinv[3] * hx + kp.Iinv[4] * hy + kp.Iinv[5] * hz;
-    const float dwz = kp.Iinv[6] * hx + kp.Iinv[7] * hy + kp.Iinv[8] * hz;
+    const T Iwx = qfma(b.wz, kp.I[2], qfma(b.wy, kp.I[1], qmul(b.wx, kp.I[0])));
+    const T Iwy = qfma(b.wz, kp.I[5], qfma(b.wy, kp.I[4], qmul(b.wx, kp.I[3])));
+    const T Iwz = qfma(b.wz, kp.I[8], qfma(b.wy, kp.I[7], qmul(b.wx, kp.I[6])));
+    const T hx = qsub(bx, qfms(b.wy, Iwz, qmul(b.wz, Iwy)));
+    const T hy = qsub(by, qfms(b.wz, Iwx, qmul(b.wx, Iwz)));
+    const T hz = qsub(bz, qfms(b.wx, Iwy, qmul(b.wy, Iwx)));
+    const T dwx = qfma(hz, kp.Iinv[2], qfma(hy, kp.Iinv[1], qmul(hx, kp.Iinv[0])));
+    const T dwy = qfma(hz, kp.Iinv[5], qfma(hy, kp.Iinv[4], qmul(hx, kp.Iinv[3])));
+    const T dwz = qfma(hz, kp.Iinv[8], qfma(hy, kp.Iinv[7], qmul(hx, kp.Iinv[6])));
     // explicit Euler, M:171-172 (all derivatives from the old state)
-    b.px = fmaf(b.vx, dt, b.px); b.py = fmaf(b.vy, dt, b.py); b.pz = fmaf(b.vz, dt, b.pz);
-    b.vx = fmaf(ax, dt, b.vx); b.vy = fmaf(ay, dt, b.vy); b.vz = fmaf(az, dt, b.vz);
-    b.roll = fmaf(droll, dt, b.roll); b.pitch = fmaf(dpitch, dt, b.pitch); b.yaw = fmaf(dyaw, dt, b.yaw);
-    b.wx = fmaf(dwx, dt, b.wx); b.wy = fmaf(dwy, dt, b.wy); b.wz = fmaf(dwz, dt, b.wz);
-    // e^T Q e on the state after the step, S:450-451 (only the non-zero diagonal entries of Q)
-    float e, c;
-    e = b.pz - ref[2]; c = (e * kp.qd[2]) * e;
-    e = b.vx - ref[3]; c = fmaf(e * kp.qd[3], e, c);
-    e = b.vy - ref[4]; c = fmaf(e * kp.qd[4], e, c);
-    e = b.vz - ref[5]; c = fmaf(e * kp.qd[5], e, c);
-    e = b.roll - ref[6]; c = fmaf(e * kp.qd[6], e, c);
-    e = b.pitch - ref[7]; c = fmaf(e * kp.qd[7], e, c);
-    e = b.wx - ref[9]; c = fmaf(e * kp.qd[9], e, c);
-    e = b.wy - ref[10]; c = fmaf(e * kp.qd[10], e, c);
-    e = b.wz - ref[11]; c = fmaf(e * kp.qd[11], e, c);
-    // the reference's Q also weights x, y (0), yaw (0): included so non-default q_diag stays exact
-    e = b.px - ref[0]; c = fmaf(e * kp.qd[0], e, c);
-    e = b.py - ref[1]; c = fmaf(e * kp.qd[1], e, c);
-    e = b.yaw - ref[8]; c = fmaf(e * kp.qd[8], e, c);
+    b.px = qfma(b.vx, dt, b.px); b.py = qfma(b.vy, dt, b.py); b.pz = qfma(b.vz, dt, b.pz);
+    b.vx = qfma(ax, dt, b.vx); b.vy = qfma(ay, dt, b.vy); b.vz = qfma(az, dt, b.vz);
+    b.roll = qfma(droll, dt, b.roll); b.pitch = qfma(dpitch, dt, b.pitch); b.yaw = qfma(dyaw, dt, b.yaw);
+    b.wx = qfma(dwx, dt, b.wx); b.wy = qfma(dwy, dt, b.wy); b.wz = qfma(dwz, dt, b.wz);
+    // e^T Q e on the state after the step, S:450-451 (diagonal Q; fixed term order)
+    T c = qset<T>(0.0f);
+    cost_term(c, b.pz, ref[2], kp.qd[2]);
+    cost_term(c, b.vx, ref[3], kp.qd[3]);
+    cost_term(c, b.vy, ref[4], kp.qd[4]);
+    cost_term(c, b.vz, ref[5], kp.qd[5]);
+    cost_term(c, b.roll, ref[6], kp.qd[6]);
+    cost_term(c, b.pitch, ref[7], kp.qd[7]);
+    cost_term(c, b.wx, ref[9], kp.qd[9]);
+    cost_term(c, b.wy, ref[10], kp.qd[10]);
+    cost_term(c, b.wz, ref[11], kp.qd[11]);
+    cost_term(c, b.px, ref[0], kp.qd[0]);
+    cost_term(c, b.py, ref[1], kp.qd[1]);
+    cost_term(c, b.yaw, ref[8], kp.qd[8]);
     return c;
 }
 
-__device__ __forceinline__ Body load_body(const float *s) {
-    Body b;
-    b.px = s[0]; b.py = s[1]; b.pz = s[2]; b.vx = s[3]; b.vy = s[4]; b.vz = s[5];
-    b.roll = s[6]; b.pitch = s[7]; b.yaw = s[8]; b.wx = s[9]; b.wy = s[10]; b.wz = s[11];
+template <class T>
+__device__ __forceinline__ BodyT<T> load_body_t(const float *s) {
+    BodyT<T> b;
+    b.px = qset<T>(s[0]); b.py = qset<T>(s[1]); b.pz = qset<T>(s[2]); b.vx = qset<T>(s[3]); b.vy = qset<T>(s[4]);
+    b.vz = qset<T>(s[5]); b.roll = qset<T>(s[6]); b.pitch = qset<T>(s[7]); b.yaw = qset<T>(s[8]); b.wx = qset<T>(s[9]);
+    b.wy = qset<T>(s[10]); b.wz = qset<T>(s[11]);
     return b;
 }
+__device__ __forceinline__ Body load_body(const float *s) { return load_body_t<float>(s); }
 
 // knot j of leg l for the thread whose tile column is `tcol`: best + eps  (S:680 | S:814 | S:960)
 #define QP_KNOT(l, j) (s_best[(l) * kp.P_leg + (j)] + tcol[((l) * kp.P_leg + (j)) * TS])
 
-__device__ __forceinline__ void add_leg(const KParams &kp, const Body &b, const float *foot, float fx, float fy, float fz,
-                                        float &Fx, float &Fy, float &Fz, float &tx, float &ty, float &tz) {
-    const float rx = foot[0] - b.px, ry = foot[1] - b.py, rz = foot[2] - b.pz;
-    Fx += fx; Fy += fy; Fz += fz;
-    tx += ry * fz - rz * fy;
-    ty += rz * fx - rx * fz;
-    tz += rx * fy - ry * fx;
-}
+// Knot sources of the fixed-gait rollout: knot p of this thread's sample(s) = best[p] + eps[p]
+struct Knots1 {                       // one sample per thread: tile column `tcol`, row stride TS
+    const float *s_best, *tcol;
+    __device__ __forceinline__ float operator()(int p) const { return qadd(tcol[p * TS], s_best[p]); }
+};
 
 // Fixed-gait rollout (S:316-496): every leg's spline clock is the step n, contact table shared by all samples,
 // so the swing/stance branch is block-uniform and swing legs are skipped (their force is multiplied by 0 twice,
 // S:388-402 and M:111-116).  s_fref[n] = mass*9.81 / n_stance(n) (S:377-380).
-template <int PARAM>
-__device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s_in, const float *s_fref, const float *tcol) {
+template <int PARAM, class T, class KNOTS>
+__device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_in, const float *s_fref, const KNOTS &knot) {
     const float *s_yaw = s_fref + MAX_H;
     const int *s_cmask = reinterpret_cast<const int *>(s_fref + MAX_H + 4);   // stance mask per step (stage_inputs)
-    const float *s_best = s_in + kp.off_best;
     const float *ref = s_in + IN_REF;
     const float *feet = s_in + IN_STATE + 12;
-    Body b = load_body(s_in + IN_STATE);
-    float cost = 0.0f;
-    const int H = kp.H;
+    BodyT<T> b = load_body_t<T>(s_in + IN_STATE);
+    T cost = qset<T>(0.0f);
+    const int H = kp.H, PL = kp.P_leg;
     constexpr float third = 1.0f / 3.0f;   // forces_z / forces_x = 30/10, S:388
     // hoisted knots of the current spline chunk (cubic: k1, phi, k2, phi_next ; linear: k0, k1)
-    float ka[4][3], kb[4][3], kc[4][3], kd[4][3];
+    T ka[4][3], kb[4][3], kc[4][3], kd[4][3];
     int cur = -1;
 #pragma unroll 1
     for (int n = 0; n < H; ++n) {
@@ -388,16 +375,17 @@ __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s
 #pragma unroll
                     for (int a = 0; a < 3; ++a) {
                         if (PARAM == CUBIC) {                 // S:219-255
-                            const int s0 = 10 * idx + 4 * a;
-                            const float p0 = QP_KNOT(l, s0), p1 = QP_KNOT(l, s0 + 1), p2 = QP_KNOT(l, s0 + 2), p3 = QP_KNOT(l, s0 + 3);
+                            const int s0 = l * PL + 10 * idx + 4 * a;
+                            const T p0 = knot(s0), p1 = knot(s0 + 1), p2 = knot(s0 + 2), p3 = knot(s0 + 3);
+                            const T d10 = qsub(p1, p0), d21 = qsub(p2, p1), d32 = qsub(p3, p2);
                             ka[l][a] = p1;
-                            kb[l][a] = 0.5f * ((p2 - p1) + (p1 - p0));
+                            kb[l][a] = qmul(qadd(d21, d10), 0.5f);
                             kc[l][a] = p2;
-                            kd[l][a] = 0.5f * ((p3 - p2) + (p2 - p1));
+                            kd[l][a] = qmul(qadd(d32, d21), 0.5f);
                         } else {                              // S:196-199
-                            const int s0 = idx + (kp.ns + 1) * a;
-                            ka[l][a] = QP_KNOT(l, s0);
-                            kb[l][a] = QP_KNOT(l, s0 + 1);
+                            const int s0 = l * PL + idx + (kp.ns + 1) * a;
+                            ka[l][a] = knot(s0);
+                            kb[l][a] = knot(s0 + 1);
                         }
                     }
                 }
@@ -405,33 +393,38 @@ __device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s
         }
         const float w0 = kp.basis[n][0], w1 = kp.basis[n][1], w2 = kp.basis[n][2], w3 = kp.basis[n][3];
         const float fref = s_fref[n];
-        float Fx = 0.f, Fy = 0.f, Fz = 0.f, tx = 0.f, ty = 0.f, tz = 0.f;
-#pragma unroll
+        T Fx = qset<T>(0.f), Fy = qset<T>(0.f), Fz = qset<T>(0.f), tx = qset<T>(0.f), ty = qset<T>(0.f), tz = qset<T>(0.f);
         const int cm = s_cmask[n];
 #pragma unroll
         for (int l = 0; l < 4; ++l) {
             if (cm & (1 << l)) {
-                float fx, fy, fz;
+                T fx, fy, fz;
                 if (PARAM == CUBIC) {
-                    fx = w0 * ka[l][0] + w1 * kb[l][0] + w2 * kc[l][0] + w3 * kd[l][0];
-                    fy = w0 * ka[l][1] + w1 * kb[l][1] + w2 * kc[l][1] + w3 * kd[l][1];
-                    fz = w0 * ka[l][2] + w1 * kb[l][2] + w2 * kc[l][2] + w3 * kd[l][2];
+                    fx = qfma(kd[l][0], w3, qfma(kc[l][0], w2, qfma(kb[l][0], w1, qmul(ka[l][0], w0))));
+                    fy = qfma(kd[l][1], w3, qfma(kc[l][1], w2, qfma(kb[l][1], w1, qmul(ka[l][1], w0))));
+                    fz = qfma(kd[l][2], w3, qfma(kc[l][2], w2, qfma(kb[l][2], w1, qmul(ka[l][2], w0))));
                 } else if (PARAM == LINEAR) {
-                    fx = w0 * ka[l][0] + w1 * kb[l][0];
-                    fy = w0 * ka[l][1] + w1 * kb[l][1];
-                    fz = w0 * ka[l][2] + w1 * kb[l][2];
+                    fx = qfma(kb[l][0], w1, qmul(ka[l][0], w0));
+                    fy = qfma(kb[l][1], w1, qmul(ka[l][1], w0));
+                    fz = qfma(kb[l][2], w1, qmul(ka[l][2], w0));
                 } else {                                      // S:259-268
-                    fx = QP_KNOT(l, n); fy = QP_KNOT(l, n + H); fz = QP_KNOT(l, n + 2 * H);
+                    fx = knot(l * PL + n); fy = knot(l * PL + n + H); fz = knot(l * PL + n + 2 * H);
                 }
-                fz = fref + fz;                               // S:382-385
-                fx = fx * third; fy = fy * third;             // S:388-402 with contact == 1
+                fz = qadd(fz, fref);                          // S:382-385
+                fx = qmul(fx, third); fy = qmul(fy, third);   // S:388-402 with contact == 1
                 clamp_leg(kp, fx, fy, fz);                    // S:405-409
                 add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }
         }
-        cost += srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw);   // S:446-451,491
+        cost = qadd(cost, srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw));   // S:446-451,491
     }
     return cost;
+}
+
+template <int PARAM>
+__device__ __forceinline__ float rollout_fixed(const KParams &kp, const float *s_in, const float *s_fref, const float *tcol) {
+    const Knots1 knot{s_in + kp.off_best, tcol};
+    return rollout_fixed_t<PARAM, float>(kp, s_in, s_fref, knot);
 }
 
 // Spline with a per-thread clock (adaptive rollouts and nothing else): S:181-268 with step = n_leg, A:353-374.

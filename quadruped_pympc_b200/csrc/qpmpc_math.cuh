@@ -1,0 +1,113 @@
+// qpmpc_math.cuh -- the rollout arithmetic written ONCE for two lane types:
+//   T = float   one sample per thread (tick_kernel, tick_kernel_h, the four-lanes-per-sample kernel, the tail)
+//   T = float2  two samples per thread in packed FP32 (tick_kernel_x2, qpmpc_x2.cuh): every multiply / add / fma below
+//               becomes ONE FMUL2 / FADD2 / FFMA2 for both samples (sm_100a issues fma.rn.f32x2 as a single
+//               instruction; block-uniform scalars ride along as `.F32` broadcast operands, no packing moves).
+// Every operation is an explicit IEEE round-to-nearest intrinsic: the compiler can neither contract nor re-associate
+// them, so where this header says fma it is an fma for both lane types and where it says mul + add it stays two
+// roundings.  Result: sample i gets bit-identical costs from either kernel (tests/test_gpu_x2.py).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace qp {
+
+// ---- lane arithmetic ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float qmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float qadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float qsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float qfma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float qneg(float a) { return -a; }
+__device__ __forceinline__ float qmin(float a, float b) { return fminf(a, b); }
+__device__ __forceinline__ float qmax(float a, float b) { return fmaxf(a, b); }
+
+__device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
+__device__ __forceinline__ float2 qneg(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 qmul(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 qmul(float2 a, float b) { return __fmul2_rn(a, bc2(b)); }
+__device__ __forceinline__ float2 qmul(float a, float2 b) { return __fmul2_rn(b, bc2(a)); }
+__device__ __forceinline__ float2 qadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 qadd(float2 a, float b) { return __fadd2_rn(a, bc2(b)); }
+__device__ __forceinline__ float2 qadd(float a, float2 b) { return __fadd2_rn(b, bc2(a)); }
+__device__ __forceinline__ float2 qsub(float2 a, float2 b) { return __fadd2_rn(a, qneg(b)); }
+__device__ __forceinline__ float2 qsub(float2 a, float b) { return __fadd2_rn(a, bc2(-b)); }
+__device__ __forceinline__ float2 qsub(float a, float2 b) { return __fadd2_rn(qneg(b), bc2(a)); }
+__device__ __forceinline__ float2 qfma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 qfma(float2 a, float b, float2 c) { return __ffma2_rn(a, bc2(b), c); }
+__device__ __forceinline__ float2 qfma(float a, float2 b, float2 c) { return __ffma2_rn(b, bc2(a), c); }
+__device__ __forceinline__ float2 qfma(float2 a, float2 b, float c) { return __ffma2_rn(a, b, bc2(c)); }
+__device__ __forceinline__ float2 qfma(float a, float2 b, float c) { return __ffma2_rn(b, bc2(a), bc2(c)); }
+__device__ __forceinline__ float2 qfma(float2 a, float b, float c) { return __ffma2_rn(a, bc2(b), bc2(c)); }
+__device__ __forceinline__ float2 qmin(float2 a, float2 b) { return make_float2(fminf(a.x, b.x), fminf(a.y, b.y)); }
+__device__ __forceinline__ float2 qmax(float2 a, float2 b) { return make_float2(fmaxf(a.x, b.x), fmaxf(a.y, b.y)); }
+__device__ __forceinline__ float2 qmin(float2 a, float b) { return make_float2(fminf(a.x, b), fminf(a.y, b)); }
+__device__ __forceinline__ float2 qmax(float2 a, float b) { return make_float2(fmaxf(a.x, b), fmaxf(a.y, b)); }
+
+template <class T> __device__ __forceinline__ T qset(float s);
+template <> __device__ __forceinline__ float qset<float>(float s) { return s; }
+template <> __device__ __forceinline__ float2 qset<float2>(float s) { return make_float2(s, s); }
+
+// a * b - c  and  c - a * b  with ONE rounding
+template <class A, class B, class C> __device__ __forceinline__ auto qfms(A a, B b, C c) -> decltype(qfma(a, b, c)) { return qfma(a, b, qneg(c)); }
+template <class A, class B, class C> __device__ __forceinline__ auto qfnma(A a, B b, C c) -> decltype(qfma(a, b, c)) { return qfma(qneg(a), b, c); }
+
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float2 rcp_approx(float2 x) { return make_float2(rcp_approx(x.x), rcp_approx(x.y)); }
+
+// ---- sine / cosine -------------------------------------------------------------------------------------------
+// |x| <= pi/4 (every sane rollout): the same minimax polynomials sincosf evaluates after its range reduction, without the
+// reduction and quadrant logic (~11 instructions instead of ~35, same <= 1 ulp accuracy); larger angles (diverged
+// samples) take the library path.
+template <class T>
+__device__ __forceinline__ void sincos_poly(T x, T &sn, T &cs) {
+    const T x2 = qmul(x, x);
+    T ps = qfma(x2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ps = qfma(ps, x2, -1.6666654611e-1f);
+    sn = qfma(qmul(x, x2), ps, x);
+    T pc = qfma(x2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    pc = qfma(pc, x2, 4.166664568298827e-2f);
+    pc = qfma(pc, x2, -0.5f);
+    cs = qfma(pc, x2, 1.0f);
+}
+__device__ __forceinline__ void sincos_small(float x, float *sn, float *cs) {
+    if (fabsf(x) <= 0.78539816f) sincos_poly<float>(x, *sn, *cs);
+    else sincosf(x, sn, cs);
+}
+__device__ __forceinline__ void sincos_small(float2 x, float2 *sn, float2 *cs) {
+    if (fabsf(x.x) <= 0.78539816f && fabsf(x.y) <= 0.78539816f) sincos_poly<float2>(x, *sn, *cs);
+    else { sincos_small(x.x, &sn->x, &cs->x); sincos_small(x.y, &sn->y, &cs->y); }
+}
+
+// Yaw is unweighted and unbounded, but every sample of a tick starts from the same yaw0: sin/cos(yaw0) are computed once
+// per block (s_yaw = {yaw0, sin yaw0, cos yaw0}, stage_inputs) and each step only needs the small-angle polynomials of
+// the drift d = yaw - yaw0 plus the angle-addition identities (~16 instructions instead of sincosf's ~35, <= 2 ulp).
+__device__ __forceinline__ void sincos_yaw(float yaw, const float *s_yaw, float *sn, float *cs) {
+    const float d = qsub(yaw, s_yaw[0]);
+    if (fabsf(d) <= 0.78539816f) {
+        float sd, cd;
+        sincos_poly<float>(d, sd, cd);
+        const float s0 = s_yaw[1], c0 = s_yaw[2];
+        *sn = qfma(s0, cd, qmul(c0, sd));
+        *cs = qfms(c0, cd, qmul(s0, sd));
+    } else {
+        sincosf(yaw, sn, cs);
+    }
+}
+__device__ __forceinline__ void sincos_yaw(float2 yaw, const float *s_yaw, float2 *sn, float2 *cs) {
+    const float2 d = qsub(yaw, s_yaw[0]);
+    if (fabsf(d.x) <= 0.78539816f && fabsf(d.y) <= 0.78539816f) {
+        float2 sd, cd;
+        sincos_poly<float2>(d, sd, cd);
+        const float s0 = s_yaw[1], c0 = s_yaw[2];
+        *sn = qfma(s0, cd, qmul(c0, sd));
+        *cs = qfms(c0, cd, qmul(s0, sd));
+    } else {
+        sincos_yaw(yaw.x, s_yaw, &sn->x, &cs->x);
+        sincos_yaw(yaw.y, s_yaw, &sn->y, &cs->y);
+    }
+}
+
+}  // namespace qp

@@ -41,6 +41,9 @@ def pytest_sessionfinish(session, exitstatus):
         lines.append(f'{name}: {len(rows)} vectors checked; max|err| / (1e-4|x| + 1 ulp): median {np.median(ratios):.3f}, '
                      f'p99 {np.percentile(ratios, 99):.3f}, max {ratios.max():.3f}; {len(fb)} needed the softmax-amplification '
                      f'fallback' + (f' (worst excess {max(r[3] for r in fb):.3e})' if fb else ''))
+    for r in log:
+        if r[2]:
+            lines.append(f'  fallback: {r[0]} x{r[1]:.1f} (excess {r[3]:.2e}, held to atol {r[5]:.2e}) in {r[4]}')
     text = '\n'.join(lines)
     print('\n[parity margin] ' + text.replace('\n', '\n[parity margin] '))
     path = os.environ.get('QPMPC_PARITY_LOG')

@@ -38,6 +38,7 @@ print('columns: cost rel err max / median / share bit-equal | knots: worst |err|
 for name, robot, gait, method, param, adaptive, N in CASES:
     for lanes in (1, 14, 4):
         worst_c, med_c, exact, rk, ak, rg, ag, fb, fb_bound = 0.0, [], 0.0, 0.0, 0.0, 0.0, 0.0, 0, 0.0
+        elite_ticks, elite_bad, elite_gap, elite_pos = 0, 0, 0.0, 0
         for seed in SEEDS:
             oracle, ctrl, _ = make_pair(robot, N, control_parametrization=param, sampling_method=method,
                                         optimize_step_freq=adaptive, lanes_per_sample=lanes)
@@ -58,8 +59,23 @@ for name, robot, gait, method, param, adaptive, N in CASES:
                 fb_bound = max(fb_bound, knot_atol(ref['costs'], got['costs'], ref.get('weights'), noise))
             assert got['best_index'] == ref['best_index']
             if method == 'cem_mppi':
-                assert np.array_equal(got['elite_indices'], ref['elite_indices'])
+                # Elite indices = stable argsort(costs)[:k].  Two float32 evaluations of the same rollout differ by ~1e-7
+                # relative (above), so they can order two samples differently only where the oracle's own costs of the
+                # two are closer than that discrepancy: report every disagreement with the gap that explains it.
+                e_got, e_ref = np.asarray(got['elite_indices']), np.asarray(ref['elite_indices'])
+                elite_ticks += 1
+                if not np.array_equal(e_got, e_ref):
+                    elite_bad += 1
+                    c = ref['costs'].astype(np.float64)
+                    pos = np.nonzero(e_got != e_ref)[0]
+                    gap = float(np.max(np.abs(c[e_got[pos]] - c[e_ref[pos]]) / c[e_ref[pos]]))
+                    elite_gap = max(elite_gap, gap)
+                    elite_pos += len(pos)
+                    assert gap < 1e-5, f'elite disagreement not explained by a near-tie: gap {gap:.2e}'
             ctrl.close()
         print(f'{name:48s} lanes={lanes:2d}: cost {worst_c:.2e} / {np.mean(med_c):.2e} / {exact / len(SEEDS):5.1%} | '
               f'knots {rk:6.3f}x, {ak:.2e} | GRFs {rg:6.3f}x, {ag:.2e} | fallback {fb}/{len(SEEDS)}'
-              + (f' (atol {fb_bound:.2e})' if fb else ''), flush=True)
+              + (f' (atol {fb_bound:.2e})' if fb else '')
+              + (f' | elites exact in {elite_ticks - elite_bad}/{elite_ticks} ticks'
+                 + (f'; {elite_pos} positions differ, all near-ties of the oracle\'s own costs (rel gap <= {elite_gap:.1e})' if elite_bad else '')
+                 if elite_ticks else ''), flush=True)
