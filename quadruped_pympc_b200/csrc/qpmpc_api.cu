@@ -1664,7 +1664,15 @@ extern "C" int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in) {
     return QPMPC_OK;
 }
 
-extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms) {
+static int bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms);
+extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms) { return bench_resident(h, steps, flush_l2, ms, nullptr); }
+// the same, additionally with the HOST wall clock around every tick (launch call -> completion seen by the host; the L2
+// flush has finished before the clock starts): sees launch latency and whatever the ranks of one box contend for
+extern "C" int qpmpc_bench_resident_wall(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms) {
+    if (!wall_ms) return fail(QPMPC_ERR_INVALID, "bad argument");
+    return bench_resident(h, steps, flush_l2, ms, wall_ms);
+}
+static int bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms) {
     if (!h || !ms || steps < 1) return fail(QPMPC_ERR_INVALID, "bad argument");
     if (!h->resident_uploaded) return fail(QPMPC_ERR_STATE, "qpmpc_upload_resident has not been called");
     if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "resident benchmarking needs an unsharded handle");
@@ -1677,11 +1685,14 @@ extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, fl
     const dim3 grid(kp.nblk, h->R);
     for (int i = 0; i < steps; ++i) {
         if (flush_l2) CK(cudaMemsetAsync(h->d_flush, i & 0xff, flush_bytes, h->stream));
+        uint64_t t0 = 0;
+        if (wall_ms) { CK(cudaStreamSynchronize(h->stream)); t0 = mono_ns(); }
         CK(cudaEventRecord(h->ev0, h->stream));
         int rc = launch(h, h->tick_fn, kp, grid);
         if (rc) return rc;
         CK(cudaEventRecord(h->ev1, h->stream));
         CK(cudaEventSynchronize(h->ev1));
+        if (wall_ms) wall_ms[i] = (float)(1e-6 * (double)(mono_ns() - t0));
         CK(cudaEventElapsedTime(&ms[i], h->ev0, h->ev1));
     }
     return QPMPC_OK;

@@ -224,3 +224,40 @@ def test_shift_is_refused_for_the_gait_adaptive_controller(built):
     state_current, ref_state = _dicts(sc)
     with pytest.raises(Exception):
         ctrl.step(state_current, ref_state, sc['contact_sequence'], sc['phase_signal'], sc['nominal_step_freq'], 1)
+
+
+@pytest.mark.parametrize('case', ['mppi', 'random_sampling_adaptive', 'cem_mppi'])
+def test_replay_of_the_reference_interface_trace_matches_the_oracle(built, case):
+    """tests/golden/interface_trace.npz = the arguments that crossed the C ABI when the reference's own
+    SRBDControllerInterface (INTEGRATION.md patch applied) drove this class (tools/make_interface_trace.py,
+    tests/test_reference_interface.py).  Every recorded tick is replayed here on the GPU, in production mode, and must
+    equal the oracle on the noise / step frequencies the device exports for the recorded key."""
+    import os
+    from helpers import assert_tick_parity
+    from oracle.sampling_oracle import OracleConfig, SamplingOracle
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'interface_trace.npz'))
+    N, H, ns, par, method, adaptive, seed = [int(x) for x in z[f'{case}/config']]
+    mass, mu, gmin, gmax = z[f'{case}/mass_mu_grf']
+    robot = {15.019: 'go2', 24.637: 'aliengo'}[round(float(mass), 3)]
+    kw = dict(sampling_method=['random_sampling', 'mppi', 'cem_mppi'][method],
+              control_parametrization=['zero_order', 'linear_spline', 'cubic_spline'][par], num_parallel_computations=N,
+              optimize_step_freq=bool(adaptive), num_splines=ns, horizon=H)
+    ctrl = qp.Sampling_MPC(qp.SamplerConfig.for_robot(robot, seed=seed, **kw))
+    orc = SamplingOracle(OracleConfig.for_robot(robot, **kw))
+    cem = method == 2
+    for t in range(z[f'{case}/key'].shape[0]):
+        key = z[f'{case}/key'][t]
+        st, rf, cs, best = z[f'{case}/state'][t], z[f'{case}/reference'][t], z[f'{case}/contact_sequence'][t], z[f'{case}/best'][t]
+        sigma = z[f'{case}/sigma'][t] if cem else None
+        ph, f, osw = z[f'{case}/phase_signal'][t], float(z[f'{case}/nominal_step_freq'][t]), int(z[f'{case}/optimize_swing'][t])
+        noise = ctrl.generate_noise(key, sigma)
+        freqs = ctrl.generate_step_freqs(key, f, osw) if adaptive else None
+        ref = orc.compute_control(st, rf, cs, best, noise, sigma=sigma, timing=ph, nominal_step_frequency=f,
+                                  optimize_swing=osw, step_frequencies=freqs)
+        out = ctrl.jitted_compute_control(st, rf, cs, best, key, sigma) if cem else \
+            ctrl.jitted_compute_control(st, rf, cs, best, key, ph, f, osw)
+        got = dict(nmpc_GRFs=out[0], nmpc_predicted_state=out[2], best_control_parameters=out[3], best_cost=out[4],
+                   best_freq=out[5], costs=np.asarray(out[6]), best_index=ctrl.last_best_index)
+        if cem:
+            got['new_sigma_cem_mppi'], got['elite_indices'] = out[7], ctrl.last_elite_indices
+        assert_tick_parity(ref, got, cem=cem, noise=noise)
