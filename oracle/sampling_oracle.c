@@ -347,7 +347,7 @@ void orc_compute_control(const orc_cfg *c, const float *state, const float *ref,
 
 /* ===================================================================================================
  * Host mirror of the product's noise generator (NOT reference code; see file header).
- * Philox4x32-10 (Salmon et al., SC'11), counter = (quad | stream << 8 | robot << 9, row, tick, seed), fixed key
+ * Philox4x32-10 (Salmon et al., SC'11), counter = (oct [uniform rows: quad] | stream << 8 | robot << 9, row, tick, seed), fixed key
  * (ORC_PHILOX_K0, ORC_PHILOX_K1) -- the same convention as csrc/qpmpc_kernels.cuh.
  * =================================================================================================== */
 static inline void philox_round(uint32_t c[4], const uint32_t k[2]) {
@@ -377,23 +377,25 @@ static inline float u01_from_bits(uint32_t b) {       /* mantissa trick of jax.r
     return f - 1.0f;
 }
 
-/* Giles, "Approximating the erfinv function" (single precision) -- the polynomial XLA's erf_inv uses */
-/* Box-Muller exactly as the device does it (csrc/qpmpc_kernels.cuh box_muller), with libm in place of the SFU
- * approximations: two words -> two standard normals. */
-static inline void box_muller(uint32_t a, uint32_t b, float *z0, float *z1) {
+/* Box-Muller exactly as the device does it (csrc/qpmpc_kernels.cuh box_muller16), with libm in place of the SFU
+ * approximations: ONE word -> two normals (radius from the low 16 bits, angle from the high 16 bits), the row's scale
+ * folded into the radius constant c = -2 ln2 * s^2. */
+static inline void box_muller16(uint32_t w, float c, float *z0, float *z1) {
     union { uint32_t u; float f; } ua, ub;
-    ua.u = (a >> 9) | 0x3F800000u;
-    ub.u = (b >> 9) | 0x40000000u;
+    ua.u = ((w << 7) & 0x007fff80u) | 0x3F800000u;
+    ub.u = ((w >> 9) & 0x007fff80u) | 0x40000000u;
     float u = 2.0f - ua.f;
     float th = ub.f * 3.14159265f + -9.42477796f;
-    float r = sqrtf(-1.38629436f * log2f(u));
+    float r = sqrtf(c * log2f(u));
     *z0 = r * cosf(th);
     *z1 = r * sinf(th);
 }
 
 /* additional_random_parameters (N,P) for one tick; sigma (P) used by cem_mppi only.  Row/segment mapping:
  * random_sampling (S:647-677): rows 1..k and k+1..2k share the same normals (same key in the reference),
- * rows 2k+1.. are uniform(-s2,s2) from the same bits; mppi/cem (S:806-812,951-958): rows 1..N-1. */
+ * rows 2k+1.. are uniform(-s2,s2); mppi/cem (S:806-812,951-958): rows 1..N-1.
+ * Normal rows: one Philox block per OCT (8 knots), counter word 0 = oct | robot << 9; uniform rows: one block per quad
+ * (4 knots, 23-bit uniforms), counter word 0 = quad | robot << 9. */
 void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_t tick, const float *sigma,
                         int row_begin, int row_end, float *noise /* (row_end-row_begin, P) */) {
     const int N = c->N, P = c->P;
@@ -407,24 +409,29 @@ void orc_noise_generate(const orc_cfg *c, uint32_t seed, uint32_t robot, uint32_
             if (i >= 1 + 2 * k) { seg = 2; j = i - 1 - 2 * k; }
             else if (i >= 1 + k) { seg = 1; j = i - 1 - k; }
         }
-        for (int qd = 0; qd < P / 4; ++qd) {
-            uint32_t ctr[4] = {(uint32_t)qd | (robot << 9), (uint32_t)j, tick, seed}, key[2] = {ORC_PHILOX_K0, ORC_PHILOX_K1}, r[4];
+        const uint32_t key[2] = {ORC_PHILOX_K0, ORC_PHILOX_K1};
+        if (c->method == ORC_RANDOM_SAMPLING && seg == 2) {
+            const float s2 = c->sigma_rs[2];
+            for (int qd = 0; qd < P / 4; ++qd) {
+                uint32_t ctr[4] = {(uint32_t)qd | (robot << 9), (uint32_t)j, tick, seed}, r[4];
+                orc_philox4x32_10(ctr, key, r);
+                for (int e = 0; e < 4; ++e) {
+                    float v = u01_from_bits(r[e]) * (s2 - (-s2)) + (-s2);
+                    row[4 * qd + e] = v > -s2 ? v : -s2;
+                }
+            }
+            continue;
+        }
+        const float scale = c->method == ORC_RANDOM_SAMPLING ? c->sigma_rs[seg] : c->sigma_mppi;
+        const float bc = c->method == ORC_CEM_MPPI ? -1.38629436f : (-1.38629436f * scale) * scale;
+        for (int oc = 0; 8 * oc < P; ++oc) {
+            uint32_t ctr[4] = {(uint32_t)oc | (robot << 9), (uint32_t)j, tick, seed}, r[4];
             orc_philox4x32_10(ctr, key, r);
-            float z[4];
-            box_muller(r[0], r[1], &z[0], &z[1]);
-            box_muller(r[2], r[3], &z[2], &z[3]);
-            for (int e = 0; e < 4; ++e) {
-                int p = 4 * qd + e;
-                float v;
-                if (c->method == ORC_RANDOM_SAMPLING) {
-                    if (seg == 2) {
-                        float s2 = c->sigma_rs[2];
-                        v = u01_from_bits(r[e]) * (s2 - (-s2)) + (-s2);
-                        v = v > -s2 ? v : -s2;
-                    } else v = c->sigma_rs[seg] * z[e];
-                } else if (c->method == ORC_MPPI) v = c->sigma_mppi * z[e];
-                else v = z[e] * sigma[p];
-                row[p] = v;
+            float z[8];
+            for (int w = 0; w < 4; ++w) box_muller16(r[w], bc, &z[2 * w], &z[2 * w + 1]);
+            for (int e = 0; e < 8 && 8 * oc + e < P; ++e) {
+                const int p = 8 * oc + e;
+                row[p] = c->method == ORC_CEM_MPPI ? z[e] * sigma[p] : z[e];
             }
         }
     }

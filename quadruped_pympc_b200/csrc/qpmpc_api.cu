@@ -23,9 +23,10 @@ using namespace qp;
 // samples per launch (all robots) up to which the four-lanes-per-sample kernel is chosen automatically (measured
 // crossover on B200)
 static const long long QPMPC_QUAD_MAX_SAMPLES = 6144;    // r1g sweep: 4k -> quad 22.6 vs 24.1 us, 10k -> 26.7 vs 24.6 us
-// samples per launch (all robots) from which the two-samples-per-thread packed-FP32 kernel (qpmpc_x2.cuh) is chosen
-// automatically for fixed-gait controllers: one full wave of its 256-sample tiles on 148 SMs x 2 resident blocks
-static const long long QPMPC_X2_MIN_SAMPLES = 148ll * 2 * XS;
+// The two-samples-per-thread packed-FP32 kernel (qpmpc_x2.cuh) is opt-in (lanes_per_sample = 2), never chosen
+// automatically: measured on B200 (profiles/r2c_*, 128 robots x 10k) it executes 24 % fewer instructions per sample
+// than the sample-per-thread kernel (5 316 vs 7 024) but its 208 registers and 104 KB tile leave 8 warps per SM, issue
+// slots 45 % busy instead of 73 % -- 1.26x slower.  See DESIGN.md section 3.
 
 // ------------------------------------------------------------------------------------------------------
 // error plumbing
@@ -459,16 +460,16 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     if (lps != 0 && lps != 1 && lps != 2 && lps != 4 && lps != 14) { delete h; return fail(QPMPC_ERR_INVALID, "lanes_per_sample must be 0 (auto), 1, 2, 4 or 14"); }
     h->lanes = lps == 4 ? 4 : (lps != 0 ? 1 : ((long long)h->n_local * h->R <= QPMPC_QUAD_MAX_SAMPLES ? 4 : 1));
     // two samples per thread in packed FP32 (tick_kernel_x2): fixed gait only, and only while two 256-sample tiles fit one
-    // SM (otherwise the plain kernel keeps more warps resident).  lanes_per_sample = 2 asks for it, 0 picks it once a
-    // launch fills the machine with such tiles; requests that do not qualify fall back to the sample-per-thread kernel.
+    // SM (otherwise the plain kernel keeps more warps resident).  lanes_per_sample = 2 asks for it; requests that do not
+    // qualify fall back to the sample-per-thread kernel.
     {
         const size_t x2_in_stride = round4((size_t)IN_CONTACT + 4 * H + 2 * (size_t)h->P);
         const bool x2_ok = !cfg->adaptive && smem_floats((int)x2_in_stride, h->P, XS, XTS) * sizeof(float) <= 113 * 1024;
-        if (x2_ok && (lps == 2 || (lps == 0 && (long long)h->n_local * h->R >= QPMPC_X2_MIN_SAMPLES))) h->lanes = 2;
+        if (x2_ok && lps == 2) h->lanes = 2;
     }
     plan_blocks(h->n_local, h->lanes, &kp.iters, &kp.nblk);
     // sample per thread + noise helper threads (tick_kernel_h): one controller, one tile per block, no more blocks than SMs
-    h->helpers = (h->lanes == 1 && lps != 1 && h->R == 1 && kp.iters == 1 && kp.nblk <= 148);
+    h->helpers = (h->lanes == 1 && (lps == 0 || lps == 14) && h->R == 1 && kp.iters == 1 && kp.nblk <= 148);
     kp.elite_k = elite_k;
     kp.mode = MODE_TICK; kp.noise_mode = NOISE_PHILOX; kp.freq_injected = 0;
     kp.fused_finish = (W == 1); kp.world = W; kp.carry_best = 0;

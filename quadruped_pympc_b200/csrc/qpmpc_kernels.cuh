@@ -137,35 +137,33 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 
 __device__ __forceinline__ float u01_from_bits(uint32_t b) { return __uint_as_float((b >> 9) | 0x3F800000u) - 1.0f; }
 
-// Two standard normals from two 32-bit words (Box-Muller on the SFU: lg2 / sqrt / sin / cos approximations).
-//   radius from a:  u = 2 - [1,2)  in (0, 1]  ->  r = sqrt(-2 ln u) = sqrt(-2 ln2 * log2 u)   (|z| <= 5.65)
-//   angle  from b:  th = pi * ([2,4) - 3)  in [-pi, pi)
-// (The reference draws with jax.random.normal = sqrt(2) * erfinv(uniform); only the distribution is part of the
-//  contract -- parity tests inject or export the tensor.  This form costs ~9 instructions per normal instead of ~22.)
-__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float &z0, float &z1) {
-    const float u = 2.0f - __uint_as_float((a >> 9) | 0x3F800000u);
-    const float th = fmaf(__uint_as_float((b >> 9) | 0x40000000u), 3.14159265f, -9.42477796f);
+// Two normals from ONE 32-bit word (Box-Muller on the SFU: lg2 / sqrt / sin / cos approximations): a Philox block of
+// four words yields EIGHT normals (r2: it yielded four; the generator was 22 % of the executed instructions).
+//   radius from the low 16 bits:  u = 2 - [1,2) (step 2^-16) in [2^-16, 1]  ->  r = sqrt(c * log2 u),  c = -2 ln2 * s^2
+//                                 (the row's scale s folded into the constant);  |z| <= 4.71 s
+//   angle  from the high 16 bits: th = pi * ([2,4) - 3)  in [-pi, pi), 65 536 directions
+// (The reference draws with jax.random.normal = sqrt(2) * erfinv(uniform), resolution 2^-23, |z| <= 5.4; only the
+//  distribution is part of the contract -- parity tests inject or export the tensor; tests/test_gpu_parity.py checks
+//  moments, tail mass and a Kolmogorov-Smirnov distance of the device's own draw.)
+__device__ __forceinline__ void box_muller16(uint32_t w, float c, float &z0, float &z1) {
+    const float u = 2.0f - __uint_as_float(((w << 7) & 0x007fff80u) | 0x3F800000u);
+    const float th = fmaf(__uint_as_float(((w >> 9) & 0x007fff80u) | 0x40000000u), 3.14159265f, -9.42477796f);
     float l2, r, sn, cs;
     asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(u));
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(-1.38629436f * l2));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(c * l2));
     asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(th));
     asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(th));
     z0 = r * cs;
     z1 = r * sn;
 }
+constexpr float BM_C1 = -1.38629436f;         // -2 ln 2: unit-variance normals
 
-__device__ __forceinline__ float4 normal_quad(uint4 r) {
-    float4 z;
-    box_muller(r.x, r.y, z.x, z.y);
-    box_muller(r.z, r.w, z.z, z.w);
-    return z;
-}
-
-// One quad (4 consecutive knots) of additional_random_parameters for global row i.
+// One quad (4 consecutive knots) / one oct (8 consecutive knots = one Philox block) of additional_random_parameters
+// for global row i.
 //  random_sampling S:647-677: rows [1,1+k) s0*N, [1+k,1+2k) s1*N (same key => same normals), [1+2k,N) U(-s2,s2)
 //  mppi S:806-812: s*N on rows 1..N-1 ; cem_mppi S:951-958: N*sigma[p] ; row 0 is always zero.
 // NoiseRow: what depends on the row only (computed once per sample, outside the loop over quads).
-struct NoiseRow { uint32_t j; int seg; float scale; bool zero; };
+struct NoiseRow { uint32_t j; int seg; float scale, c; bool zero; };   // c = -2 ln2 * scale^2 (cem_mppi: -2 ln2)
 
 template <int METHOD>
 __device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
@@ -177,41 +175,62 @@ __device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
         else if (i >= 1 + k) { nr.seg = 1; nr.j = (uint32_t)(i - 1 - k); }
         nr.scale = kp.sigma_rs[nr.seg];
     }
+    nr.c = (METHOD == CEM_MPPI) ? BM_C1 : (BM_C1 * nr.scale) * nr.scale;
     return nr;
 }
 
+// uniform rows of random_sampling: one Philox block per quad, 23-bit uniforms (counter word 0 = quad index)
+__device__ __forceinline__ float4 uniform_quad(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q) {
+    const uint4 r = philox4x32_10((uint32_t)q | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
+    const float s2 = nr.scale, span = s2 - (-s2);
+    float4 v;
+    v.x = fmaxf(fmaf(u01_from_bits(r.x), span, -s2), -s2);
+    v.y = fmaxf(fmaf(u01_from_bits(r.y), span, -s2), -s2);
+    v.z = fmaxf(fmaf(u01_from_bits(r.z), span, -s2), -s2);
+    v.w = fmaxf(fmaf(u01_from_bits(r.w), span, -s2), -s2);
+    return v;
+}
+// four normals of a row from two words of its Philox block; knots 4q .. 4q+3 (cem_mppi: times sigma[p])
 template <int METHOD>
-__device__ __forceinline__ float4 noise_quad_nz(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
-                                                const float *s_sigma);
+__device__ __forceinline__ float4 normal_quad(const NoiseRow &nr, uint32_t w0, uint32_t w1, int q, const float *s_sigma) {
+    float4 v;
+    box_muller16(w0, nr.c, v.x, v.y);
+    box_muller16(w1, nr.c, v.z, v.w);
+    if (METHOD == CEM_MPPI) {
+        v.x *= s_sigma[4 * q + 0]; v.y *= s_sigma[4 * q + 1]; v.z *= s_sigma[4 * q + 2]; v.w *= s_sigma[4 * q + 3];
+    }
+    return v;
+}
+
+// Oct c of a row >= 1 (the caller has dealt with the all-zero row 0): quads 2c (lo) and 2c+1 (hi) from ONE Philox block,
+// counter = (c | robot << 9, row, tick, seed).  `hi` is meaningless when 2c+1 is not a quad of the row (P/4 odd).
+template <int METHOD>
+__device__ __forceinline__ void noise_oct_nz(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int c,
+                                             const float *s_sigma, float4 &lo, float4 &hi) {
+    if (METHOD == RANDOM_SAMPLING && nr.seg == 2) {
+        lo = uniform_quad(nr, seed, robot, tick, 2 * c);
+        hi = uniform_quad(nr, seed, robot, tick, 2 * c + 1);
+        return;
+    }
+    const uint4 r = philox4x32_10((uint32_t)c | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
+    lo = normal_quad<METHOD>(nr, r.x, r.y, 2 * c, s_sigma);
+    hi = normal_quad<METHOD>(nr, r.z, r.w, 2 * c + 1, s_sigma);
+}
+template <int METHOD>
+__device__ __forceinline__ void noise_oct(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int c,
+                                          const float *s_sigma, float4 &lo, float4 &hi) {
+    if (nr.zero) { lo = make_float4(0.f, 0.f, 0.f, 0.f); hi = lo; return; }
+    noise_oct_nz<METHOD>(nr, seed, robot, tick, c, s_sigma, lo, hi);
+}
+
+// one quad alone (finish stage, export kernels): half of its oct
 template <int METHOD>
 __device__ __forceinline__ float4 noise_quad(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
                                              const float *s_sigma) {
     if (nr.zero) return make_float4(0.f, 0.f, 0.f, 0.f);
-    return noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
-}
-// rows >= 1 (the caller has dealt with the all-zero row 0 outside its loop over quads)
-template <int METHOD>
-__device__ __forceinline__ float4 noise_quad_nz(const NoiseRow &nr, uint32_t seed, uint32_t robot, uint32_t tick, int q,
-                                                const float *s_sigma) {
-    uint4 r = philox4x32_10((uint32_t)q | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
-    float4 v;
-    if (METHOD == RANDOM_SAMPLING && nr.seg == 2) {
-        const float s2 = nr.scale;
-        const float span = s2 - (-s2);
-        v.x = fmaxf(fmaf(u01_from_bits(r.x), span, -s2), -s2);
-        v.y = fmaxf(fmaf(u01_from_bits(r.y), span, -s2), -s2);
-        v.z = fmaxf(fmaf(u01_from_bits(r.z), span, -s2), -s2);
-        v.w = fmaxf(fmaf(u01_from_bits(r.w), span, -s2), -s2);
-    } else if (METHOD == CEM_MPPI) {
-        const float4 z = normal_quad(r);
-        v.x = z.x * s_sigma[4 * q + 0]; v.y = z.y * s_sigma[4 * q + 1];
-        v.z = z.z * s_sigma[4 * q + 2]; v.w = z.w * s_sigma[4 * q + 3];
-    } else {
-        const float s = nr.scale;
-        const float4 z = normal_quad(r);
-        v.x = s * z.x; v.y = s * z.y; v.z = s * z.z; v.w = s * z.w;
-    }
-    return v;
+    if (METHOD == RANDOM_SAMPLING && nr.seg == 2) return uniform_quad(nr, seed, robot, tick, q);
+    const uint4 r = philox4x32_10((uint32_t)(q >> 1) | (robot << 9), nr.j, tick, seed, PHILOX_K0, PHILOX_K1);
+    return (q & 1) ? normal_quad<METHOD>(nr, r.z, r.w, q, s_sigma) : normal_quad<METHOD>(nr, r.x, r.y, q, s_sigma);
 }
 // convenience form for one-off rows (finish stage, export kernels)
 template <int METHOD>
@@ -266,11 +285,12 @@ __device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, co
     tz = qadd(tz, qfms(rx, fy, qmul(ry, fx)));
 }
 
-// one term of e^T Q e on the state after the step, S:450-451.  Zero weights (x, y, yaw with the reference's Q) are
-// skipped by a block-uniform branch: (e * 0) * e adds exactly nothing for every finite e.
+// one term of e^T Q e on the state after the step, S:450-451 (the reference's Q also weights x, y, yaw with 0: kept, so
+// that a non-default q_diag stays exact; a test-and-branch per term costs more than the three instructions it skips)
 template <class T>
 __device__ __forceinline__ void cost_term(T &c, T x, float ref, float q) {
-    if (q != 0.0f) { const T e = qsub(x, ref); c = qfma(qmul(e, q), e, c); }
+    const T e = qsub(x, ref);
+    c = qfma(qmul(e, q), e, c);
 }
 
 template <class T>
@@ -278,9 +298,7 @@ __device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T F
                                        const float *ref, const float *s_yaw) {
     const T ax = qmul(Fx, kp.inv_m), ay = qmul(Fy, kp.inv_m), az = qfma(Fz, kp.inv_m, -9.81f);       // M:118
     T sr, cr, sp, cp, sy, cy;
-    sincos_small(b.roll, &sr, &cr);
-    sincos_small(b.pitch, &sp, &cp);
-    sincos_yaw(b.yaw, s_yaw, &sy, &cy);
+    sincos_rpy(b.roll, b.pitch, b.yaw, s_yaw, sr, cr, sp, cp, sy, cy);
     // inverse of the conjugate Euler-rate matrix by cofactors with its structural zeros dropped, M:124-130,137
     const T cpcr = qmul(cp, cr), cpsr = qmul(cp, sr), srsp = qmul(sr, sp), crsp = qmul(cr, sp);
     const T det = qfma(sr, cpsr, qmul(cpcr, cr));
@@ -313,8 +331,8 @@ __device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T F
     b.roll = qfma(droll, dt, b.roll); b.pitch = qfma(dpitch, dt, b.pitch); b.yaw = qfma(dyaw, dt, b.yaw);
     b.wx = qfma(dwx, dt, b.wx); b.wy = qfma(dwy, dt, b.wy); b.wz = qfma(dwz, dt, b.wz);
     // e^T Q e on the state after the step, S:450-451 (diagonal Q; fixed term order)
-    T c = qset<T>(0.0f);
-    cost_term(c, b.pz, ref[2], kp.qd[2]);
+    T c;
+    { const T e = qsub(b.pz, ref[2]); c = qmul(qmul(e, kp.qd[2]), e); }
     cost_term(c, b.vx, ref[3], kp.qd[3]);
     cost_term(c, b.vy, ref[4], kp.qd[4]);
     cost_term(c, b.vz, ref[5], kp.qd[5]);

@@ -110,4 +110,31 @@ __device__ __forceinline__ void sincos_yaw(float2 yaw, const float *s_yaw, float
     }
 }
 
+// One range test for the three angles of a step (roll, pitch, yaw drift): a single branch around three polynomial
+// evaluations instead of three test-and-branch diamonds.  Same results: the fast path is the polynomials above, the slow
+// path re-tests each angle on its own.
+__device__ __forceinline__ bool angles_small(float a, float b, float c) {
+    return fmaxf(fmaxf(fabsf(a), fabsf(b)), fabsf(c)) <= 0.78539816f;
+}
+__device__ __forceinline__ bool angles_small(float2 a, float2 b, float2 c) {
+    return fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(b.x), fabsf(b.y))), fmaxf(fabsf(c.x), fabsf(c.y))) <= 0.78539816f;
+}
+template <class T>
+__device__ __forceinline__ void sincos_rpy(T roll, T pitch, T yaw, const float *s_yaw, T &sr, T &cr, T &sp, T &cp, T &sy, T &cy) {
+    const T d = qsub(yaw, s_yaw[0]);
+    if (angles_small(roll, pitch, d)) {
+        T sd, cd;
+        sincos_poly<T>(roll, sr, cr);
+        sincos_poly<T>(pitch, sp, cp);
+        sincos_poly<T>(d, sd, cd);
+        const float s0 = s_yaw[1], c0 = s_yaw[2];
+        sy = qfma(s0, cd, qmul(c0, sd));
+        cy = qfms(c0, cd, qmul(s0, sd));
+    } else {
+        sincos_small(roll, &sr, &cr);
+        sincos_small(pitch, &sp, &cp);
+        sincos_yaw(yaw, s_yaw, &sy, &cy);
+    }
+}
+
 }  // namespace qp

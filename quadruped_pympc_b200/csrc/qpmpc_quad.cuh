@@ -206,8 +206,8 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     float m_run = CUDART_INF_F, s_run = 0.0f;
     int idx_run = 0x7fffffff;
     for (int p = t; p < kp.P; p += QTB) s.v[p] = 0.0f;
-    const int nq = kp.P >> 2;
-    const int q_lo = (leg * nq) >> 2, q_hi = ((leg + 1) * nq) >> 2;   // this lane's share of the sample's noise quads
+    const int nq = kp.P >> 2, noct = (nq + 1) >> 1;
+    const int c_lo = (leg * noct) >> 2, c_hi = ((leg + 1) * noct) >> 2;   // this lane's share of the sample's noise octs (Philox blocks)
 
     for (int it = 0; it < kp.iters; ++it) {
         const int tile_base = (blk * kp.iters + it) * QS;
@@ -225,17 +225,15 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             }
             __syncthreads();
         } else {
-            if (active && gi != 0) {
-                const NoiseRow nr = noise_row<METHOD>(kp, gi);
+            NoiseRow nr = noise_row<METHOD>(kp, gi);
+            nr.zero = nr.zero || !active;
 #pragma unroll 2
-                for (int q = q_lo; q < q_hi; ++q) {
-                    const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
-                    tcol[(4 * q) * QTS] = e.x; tcol[(4 * q + 1) * QTS] = e.y; tcol[(4 * q + 2) * QTS] = e.z; tcol[(4 * q + 3) * QTS] = e.w;
-                }
-            } else {
-                for (int q = q_lo; q < q_hi; ++q) {
-                    tcol[(4 * q) * QTS] = 0.f; tcol[(4 * q + 1) * QTS] = 0.f; tcol[(4 * q + 2) * QTS] = 0.f; tcol[(4 * q + 3) * QTS] = 0.f;
-                }
+            for (int c = c_lo; c < c_hi; ++c) {
+                float4 lo, hi;
+                noise_oct<METHOD>(nr, seed, robot, tick, c, s_sigma, lo, hi);
+                float *tp = tcol + 8 * c * QTS;
+                tp[0] = lo.x; tp[QTS] = lo.y; tp[2 * QTS] = lo.z; tp[3 * QTS] = lo.w;
+                if (2 * c + 1 < nq) { tp[4 * QTS] = hi.x; tp[5 * QTS] = hi.y; tp[6 * QTS] = hi.z; tp[7 * QTS] = hi.w; }
             }
             __syncwarp();                                        // the four lanes of a quad live in one warp
         }

@@ -6,7 +6,7 @@
 namespace qp {
 
 constexpr int MAXV = 6;                 // P <= MAXV * TB knots
-static_assert(MAXV * TB / 4 <= 256, "the quad index must fit bits 0-7 of Philox counter word 0 (qpmpc_kernels.cuh noise_quad_nz)");
+static_assert(MAXV * TB / 4 <= 256, "the quad index must fit bits 0-7 of Philox counter word 0 (qpmpc_kernels.cuh uniform_quad / noise_oct_nz)");
 constexpr int SCRATCH_KEYS = 2048;      // u64 keys for the cross-shard elite merge (world * elite_k <= 2048)
 constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogram + misc
 
@@ -396,10 +396,15 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
                 const float *row = kp.noise + ((size_t)r * kp.N + my_idx) * kp.P;
                 for (int p = 0; p < kp.P; ++p) tcol[p * TS] = __ldg(row + p);
             } else {
-#pragma unroll 4
-                for (int q = 0; q < kp.P / 4; ++q) {                // independent Philox chains: unrolled for ILP (4 warps alone on the SM)
-                    const float4 e = noise_quad<METHOD>(kp, seed, robot, tick, my_idx, q, s_sigma);
-                    tcol[(4 * q) * TS] = e.x; tcol[(4 * q + 1) * TS] = e.y; tcol[(4 * q + 2) * TS] = e.z; tcol[(4 * q + 3) * TS] = e.w;
+                const NoiseRow nr = noise_row<METHOD>(kp, my_idx);
+                const int nq = kp.P >> 2, noct = (nq + 1) >> 1;
+#pragma unroll 2
+                for (int c = 0; c < noct; ++c) {                    // independent Philox chains: unrolled for ILP (4 warps alone on the SM)
+                    float4 lo, hi;
+                    noise_oct<METHOD>(nr, seed, robot, tick, c, s_sigma, lo, hi);
+                    float *tp = tcol + 8 * c * TS;
+                    tp[0] = lo.x; tp[TS] = lo.y; tp[2 * TS] = lo.z; tp[3 * TS] = lo.w;
+                    if (2 * c + 1 < nq) { tp[4 * TS] = hi.x; tp[5 * TS] = hi.y; tp[6 * TS] = hi.z; tp[7 * TS] = hi.w; }
                 }
             }
         }
@@ -621,11 +626,14 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
         } else {
             if (active && gi != 0) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
-                float *tp = tcol + hlp * 4 * TS;
-#pragma unroll 4
-                for (int q = hlp; q < kp.P / 4; q += NH, tp += NH * 4 * TS) {
-                    const float4 e = noise_quad_nz<METHOD>(nr, seed, robot, tick, q, s_sigma);
-                    tp[0] = e.x; tp[TS] = e.y; tp[2 * TS] = e.z; tp[3 * TS] = e.w;
+                const int nq = kp.P >> 2, noct = (nq + 1) >> 1;      // one Philox block per oct (8 knots)
+                float *tp = tcol + hlp * 8 * TS;
+#pragma unroll 2
+                for (int c = hlp; c < noct; c += NH, tp += NH * 8 * TS) {
+                    float4 lo, hi;
+                    noise_oct_nz<METHOD>(nr, seed, robot, tick, c, s_sigma, lo, hi);
+                    tp[0] = lo.x; tp[TS] = lo.y; tp[2 * TS] = lo.z; tp[3 * TS] = lo.w;
+                    if (2 * c + 1 < nq) { tp[4 * TS] = hi.x; tp[5 * TS] = hi.y; tp[6 * TS] = hi.z; tp[7 * TS] = hi.w; }
                 }
             } else {                                            // padding rows and row 0 (the previous best re-evaluated)
                 for (int p = hlp; p < kp.P; p += NH) tcol[p * TS] = 0.0f;

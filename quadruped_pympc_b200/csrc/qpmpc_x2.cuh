@@ -87,14 +87,21 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
             nr0.zero = nr0.zero || !act0;                       // row 0 (the previous best re-evaluated) and padding rows
             nr1.zero = nr1.zero || !act1;
             float *tp = tpair;
-#pragma unroll 2
-            for (int q = 0; q < kp.P / 4; ++q, tp += 4 * XTS) {
-                const float4 e0 = noise_quad<METHOD>(nr0, seed, robot, tick, q, s_sigma);
-                const float4 e1 = noise_quad<METHOD>(nr1, seed, robot, tick, q, s_sigma);
-                *reinterpret_cast<float2 *>(tp) = make_float2(e0.x, e1.x);
-                *reinterpret_cast<float2 *>(tp + XTS) = make_float2(e0.y, e1.y);
-                *reinterpret_cast<float2 *>(tp + 2 * XTS) = make_float2(e0.z, e1.z);
-                *reinterpret_cast<float2 *>(tp + 3 * XTS) = make_float2(e0.w, e1.w);
+            const int nq = kp.P >> 2, noct = (nq + 1) >> 1;
+            for (int c = 0; c < noct; ++c, tp += 8 * XTS) {
+                float4 a0, b0, a1, b1;
+                noise_oct<METHOD>(nr0, seed, robot, tick, c, s_sigma, a0, b0);
+                noise_oct<METHOD>(nr1, seed, robot, tick, c, s_sigma, a1, b1);
+                *reinterpret_cast<float2 *>(tp) = make_float2(a0.x, a1.x);
+                *reinterpret_cast<float2 *>(tp + XTS) = make_float2(a0.y, a1.y);
+                *reinterpret_cast<float2 *>(tp + 2 * XTS) = make_float2(a0.z, a1.z);
+                *reinterpret_cast<float2 *>(tp + 3 * XTS) = make_float2(a0.w, a1.w);
+                if (2 * c + 1 < nq) {
+                    *reinterpret_cast<float2 *>(tp + 4 * XTS) = make_float2(b0.x, b1.x);
+                    *reinterpret_cast<float2 *>(tp + 5 * XTS) = make_float2(b0.y, b1.y);
+                    *reinterpret_cast<float2 *>(tp + 6 * XTS) = make_float2(b0.z, b1.z);
+                    *reinterpret_cast<float2 *>(tp + 7 * XTS) = make_float2(b0.w, b1.w);
+                }
             }
         }
         if (blk == 0 && it == 0) phase_mark(kp, 2);

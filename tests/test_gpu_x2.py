@@ -55,7 +55,7 @@ def test_x2_costs_are_bit_identical_to_the_sample_per_thread_kernel(built, param
             break                                                   # the second tick starts from (slightly) different knots
 
 
-def test_x2_is_chosen_for_large_fixed_gait_launches_only(built):
+def test_x2_is_opt_in_and_fixed_gait_only(built):
     def name(N, lanes=0, robots=None, **kw):
         cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', num_parallel_computations=N, lanes_per_sample=lanes, **kw)
         if robots is None:
@@ -63,21 +63,17 @@ def test_x2_is_chosen_for_large_fixed_gait_launches_only(built):
         from quadruped_pympc_b200 import _lib
         return _lib.load().qpmpc_kernel_name(BatchedSampling_MPC(cfg, robots)._ensure()).decode()
 
-    assert name(148 * 2 * 256) == 'tick_kernel_x2' and name(148 * 2 * 256 - 1) == 'tick_kernel'
-    assert name(10000, robots=8) == 'tick_kernel_x2' and name(10000, robots=7) == 'tick_kernel'
-    assert name(1000000) == 'tick_kernel_x2'
-    assert name(1000000, optimize_step_freq=True) == 'tick_kernel'                 # gait-adaptive: not packed
-    assert name(5000, lanes=2) == 'tick_kernel_x2' and name(5000, lanes=2, optimize_step_freq=True) == 'tick_kernel'
+    assert name(1000000) == 'tick_kernel' and name(10000, robots=8) == 'tick_kernel'   # never picked automatically (slower)
+    assert name(5000, lanes=2) == 'tick_kernel_x2' and name(10000, lanes=2, robots=8) == 'tick_kernel_x2'
+    assert name(5000, lanes=2, optimize_step_freq=True) == 'tick_kernel'                 # gait-adaptive: not packed
     assert name(100000, lanes=2, control_parametrization='zero_order') == 'tick_kernel'   # P = 144: two tiles do not fit one SM
-    assert name(100000, lanes=1) == 'tick_kernel'
 
 
 def test_x2_batched_robots_equal_the_per_robot_kernel(built):
-    """8 robots x 10k = the launch shape the auto rule hands to tick_kernel_x2; per robot the costs must be the bits the
-    sample-per-thread kernel produces for that robot."""
+    """8 robots x 10k in one packed launch: per robot the costs must be the bits the sample-per-thread kernel produces."""
     R, N = 8, 10000
     out = {}
-    for lanes in (1, 0):
+    for lanes in (1, 2):
         cfg = qp.SamplerConfig.for_robot('go2', sampling_method='mppi', control_parametrization='cubic_spline',
                                          num_parallel_computations=N, lanes_per_sample=lanes)
         b = BatchedSampling_MPC(cfg, R, robot_base=5)
@@ -89,6 +85,6 @@ def test_x2_batched_robots_equal_the_per_robot_kernel(built):
         res = b.compute_control(st, rf, cs, np.zeros((R, 96), np.float32))
         out[lanes] = (res, [b.fetch_costs(r) for r in range(R)])
     for r in range(R):
-        np.testing.assert_array_equal(out[0][1][r], out[1][1][r])
-    np.testing.assert_array_equal(out[0][0][5], out[1][0][5])            # best indices
-    np.testing.assert_allclose(out[0][0][2], out[1][0][2], rtol=1e-4, atol=2e-5)
+        np.testing.assert_array_equal(out[2][1][r], out[1][1][r])
+    np.testing.assert_array_equal(out[2][0][5], out[1][0][5])            # best indices
+    np.testing.assert_allclose(out[2][0][2], out[1][0][2], rtol=1e-4, atol=2e-5)

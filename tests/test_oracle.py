@@ -39,6 +39,37 @@ def test_noise_mirror_layout_and_moments(built):
     assert not np.array_equal(nz, c_oracle.COracle(cfg).noise(42, 1, robot=1))  # so does the robot id
 
 
+def _normal_distribution_checks(z):
+    """z: (rows, P) standard normals as the generator lays them out (8 per Philox block, two per 32-bit word)."""
+    from scipy import stats
+    flat = z.ravel()
+    n = flat.size
+    assert abs(flat.mean()) < 4.0 / np.sqrt(n) and abs(flat.std() - 1.0) < 4.0 / np.sqrt(2 * n)
+    assert abs(np.mean(flat ** 4) - 3.0) < 0.03                                  # kurtosis of a normal
+    d, _ = stats.kstest(flat[:2000000], 'norm')
+    assert d < 1.63 / np.sqrt(min(n, 2000000))                                   # Kolmogorov-Smirnov, alpha = 0.01
+    assert np.max(np.abs(flat)) <= 4.72                                          # 16-bit radius: |z| <= sqrt(32 ln 2)
+    tail = np.mean(np.abs(flat) > 3.0)
+    assert abs(tail - 0.0026998) < 4 * np.sqrt(0.0027 / n)                       # mass beyond 3 sigma
+    # the eight normals of one block (and the two of one word) are uncorrelated, also in their squares
+    oct = z[:, :8 * (z.shape[1] // 8)].reshape(-1, 8)
+    c1 = np.corrcoef(oct, rowvar=False) - np.eye(8)
+    c2 = np.corrcoef(oct ** 2, rowvar=False) - np.eye(8)
+    assert np.max(np.abs(c1)) < 5.0 / np.sqrt(oct.shape[0]) and np.max(np.abs(c2)) < 5.0 / np.sqrt(oct.shape[0])
+    # consecutive rows (counter word 1 differs by one) are uncorrelated
+    assert abs(np.corrcoef(z[:-1].ravel(), z[1:].ravel())[0, 1]) < 5.0 / np.sqrt(n)
+
+
+def test_noise_mirror_is_standard_normal(built):
+    """The generator draws 8 normals per Philox4x32-10 block (16-bit radius, 16-bit angle per Box-Muller pair): moments,
+    Kolmogorov-Smirnov distance, tail mass and independence inside a block of the host mirror (the device kernel is held
+    to the mirror within 2e-4 in tests/test_gpu_parity.py, and runs the same checks on its own draw)."""
+    cfg = OracleConfig.for_robot('go2', sampling_method='mppi', control_parametrization='cubic_spline',
+                                 num_parallel_computations=30001)
+    z = c_oracle.COracle(cfg).noise(42, 3)[1:] / np.float32(3.0)
+    _normal_distribution_checks(z)
+
+
 @pytest.mark.parametrize('param', PARAMS)
 def test_zero_noise_row_reproduces_cost_of_best(param):
     """Row 0 of the noise is zero, so costs[0] is the cost of the previous best (S:647)."""
