@@ -1,8 +1,10 @@
 // sample-per-thread tick kernel + shard finish kernel, parametrisation CUBIC
 #include "qpmpc_inst.cuh"
 #include "qpmpc_tick.cuh"
-extern "C" void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]) {
+#include "qpmpc_tail.cuh"
+extern "C" void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3], qp::KernelFn tail[2][3]) {
     QP_FILL(tick, tick_kernel, qp::CUBIC)
     QP_FILL(fin, finish_kernel, qp::CUBIC)
     QP_FILL(tick_h, tick_kernel_h, qp::CUBIC)
+    QP_FILL(tail, tail_kernel, qp::CUBIC)
 }

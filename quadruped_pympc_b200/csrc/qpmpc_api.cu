@@ -4,6 +4,7 @@
 #include "qpmpc_inst.cuh"
 #include "qpmpc_quad.cuh"
 #include "qpmpc_x2.cuh"
+#include "qpmpc_tail.cuh"
 
 #include <dlfcn.h>
 #include <unistd.h>
@@ -23,6 +24,10 @@ using namespace qp;
 // samples per launch (all robots) up to which the four-lanes-per-sample kernel is chosen automatically (measured
 // crossover on B200)
 static const long long QPMPC_QUAD_MAX_SAMPLES = 6144;    // r1g sweep: 4k -> quad 22.6 vs 24.1 us, 10k -> 26.7 vs 24.6 us
+// block records per robot from which the reduction tail runs as a second, multi-block kernel (qpmpc_tail.cuh) instead of
+// in the tick kernel's last block: 192 records = 24 576 samples per controller (one 10k..18k-sample controller keeps the
+// single fused launch -- its tail is short and a second launch would cost more than it saves)
+static const int QPMPC_TAIL_MIN_BLOCKS = 192;
 // The two-samples-per-thread packed-FP32 kernel (qpmpc_x2.cuh) is opt-in (lanes_per_sample = 2), never chosen
 // automatically: measured on B200 (profiles/r2c_*, 128 robots x 10k) it executes 24 % fewer instructions per sample
 // than the sample-per-thread kernel (5 316 vs 7 024) but its 208 registers and 104 KB tile leave 8 warps per SM, issue
@@ -196,11 +201,11 @@ __global__ void fp32_peak_kernel(float *out, int iters, float a, float b) {
 // ------------------------------------------------------------------------------------------------------
 // kernel dispatch tables (parametrisation x adaptive x method)
 // ------------------------------------------------------------------------------------------------------
-static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3], g_x2_table[3][3];
+static KernelFn g_tick_table[3][2][3], g_finish_table[3][2][3], g_quad_table[3][2][3], g_tick_h_table[3][2][3], g_x2_table[3][3], g_tail_table[3][2][3];
 static void fill_kernel_tables_once() {
-    qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER], g_tick_h_table[ZERO_ORDER]);
-    qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR], g_tick_h_table[LINEAR]);
-    qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC], g_tick_h_table[CUBIC]);
+    qp_inst_tick_zero(g_tick_table[ZERO_ORDER], g_finish_table[ZERO_ORDER], g_tick_h_table[ZERO_ORDER], g_tail_table[ZERO_ORDER]);
+    qp_inst_tick_linear(g_tick_table[LINEAR], g_finish_table[LINEAR], g_tick_h_table[LINEAR], g_tail_table[LINEAR]);
+    qp_inst_tick_cubic(g_tick_table[CUBIC], g_finish_table[CUBIC], g_tick_h_table[CUBIC], g_tail_table[CUBIC]);
     qp_inst_quad_zero(g_quad_table[ZERO_ORDER]);
     qp_inst_quad_linear(g_quad_table[LINEAR]);
     qp_inst_quad_cubic(g_quad_table[CUBIC]);
@@ -267,7 +272,11 @@ struct qpmpc_handle {
     uint64_t launches = 0;
     bool resident_uploaded = false, partial_done = false;
     NcclComm comm = nullptr;
-    KernelFn tick_fn = nullptr, finish_fn = nullptr;
+    KernelFn tick_fn = nullptr, finish_fn = nullptr, tail_fn = nullptr;
+    int tail_nb = 0;                  // > 0: two-stage launches (tick kernel + tail_kernel with tail_nb blocks per robot)
+    float *d_part = nullptr;
+    unsigned int *d_tail_cnt = nullptr;
+    unsigned long long *d_tail_keys = nullptr;
     int threads = TB;                 // threads per block of tick_fn (finish_fn always runs TB)
     bool helpers = false;             // tick_fn = tick_kernel_h (sample per thread + noise helper threads)
     bool direct = false;              // QPMPC_IO_DIRECT in effect
@@ -380,6 +389,7 @@ static void free_handle(qpmpc_handle *h) {
     }
     for (int w = 0; w < MAX_PEERS; ++w)
         if (h->peer_ipc[w] && h->peer_mbox[w]) cudaIpcCloseMemHandle(h->peer_mbox[w]);
+    cudaFree(h->d_part); cudaFree(h->d_tail_cnt); cudaFree(h->d_tail_keys);
     cudaFree(h->d_mbox); cudaFree(h->d_sink); cudaFree(h->d_ctrl); cudaFree(h->d_epi); cudaFree(h->d_contact); cudaFree(h->d_pgg); cudaFree(h->d_frg);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->stream2) cudaStreamDestroy(h->stream2);
@@ -525,9 +535,12 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->tick_fn = h->lanes == 2 ? g_x2_table[cfg->parametrization][cfg->method]
                                : (h->lanes == 4 ? g_quad_table : (h->helpers ? g_tick_h_table : g_tick_table))[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    h->tail_fn = g_tail_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
+    if (kp.nblk >= QPMPC_TAIL_MIN_BLOCKS) h->tail_nb = std::max(1, std::min(TAIL_MAX_NB, 296 / h->R));
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
+    CKH(cudaFuncSetAttribute((const void *)h->tail_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
     CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
@@ -547,6 +560,13 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
     CKH(cudaMalloc((void **)&h->d_sigma, (size_t)h->P * sizeof(float)));
     CKH(cudaMemset(h->d_counters, 0, R * sizeof(unsigned int)));
+    if (h->tail_nb > 0) {
+        CKH(cudaMalloc((void **)&h->d_part, R * (size_t)h->tail_nb * kp.blk_rec_stride * sizeof(float)));
+        CKH(cudaMalloc((void **)&h->d_tail_cnt, R * tail_cnt_stride() * sizeof(unsigned int)));
+        CKH(cudaMemset(h->d_tail_cnt, 0, R * tail_cnt_stride() * sizeof(unsigned int)));
+        if (cfg->method == QPMPC_CEM_MPPI) CKH(cudaMalloc((void **)&h->d_tail_keys, R * 2 * (size_t)h->n_local * sizeof(unsigned long long)));
+        kp.tail_nb = h->tail_nb; kp.part_recs = h->d_part; kp.tail_cnt = h->d_tail_cnt; kp.tail_keys = h->d_tail_keys;
+    }
     if (cfg->method == QPMPC_CEM_MPPI) {       // per-robot cost histogram: zero between ticks (the last block re-zeroes it)
         CKH(cudaMalloc((void **)&h->d_cem_hist, R * (size_t)CEM_BINS * sizeof(unsigned int)));
         CKH(cudaMemset(h->d_cem_hist, 0, R * (size_t)CEM_BINS * sizeof(unsigned int)));
@@ -653,10 +673,21 @@ static int ensure_freqs(qpmpc_handle *h, size_t floats) {
 }
 
 static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid, cudaStream_t stream = nullptr) {
-    void *args[] = {(void *)&kp};
     const bool is_finish = (fn == h->finish_fn);
+    cudaStream_t st = stream ? stream : h->stream;
+    if (!is_finish && h->tail_nb > 0 && kp.mode == MODE_TICK) {
+        // large launch: the tick kernel stops after its block records, tail_kernel (multi-block) finishes the tick
+        KParams k2 = kp;
+        k2.defer_tail = 1;
+        void *args[] = {(void *)&k2};
+        CK(cudaLaunchKernel((const void *)fn, grid, dim3(h->threads), args, h->smem_bytes, st));
+        CK(cudaLaunchKernel((const void *)h->tail_fn, dim3(h->tail_nb, grid.y), dim3(TB), args, h->finish_smem_bytes, st));
+        h->launches += 2;
+        return QPMPC_OK;
+    }
+    void *args[] = {(void *)&kp};
     CK(cudaLaunchKernel((const void *)fn, grid, dim3(is_finish ? TB : h->threads), args,
-                        is_finish ? h->finish_smem_bytes : h->smem_bytes, stream ? stream : h->stream));
+                        is_finish ? h->finish_smem_bytes : h->smem_bytes, st));
     h->launches++;
     return QPMPC_OK;
 }
@@ -912,6 +943,9 @@ static void offset_robots(KParams &kp, int r0) {
     if (kp.cem_hist) kp.cem_hist += (size_t)r0 * CEM_BINS;
     if (kp.contact_dev) kp.contact_dev += (size_t)r0 * 4 * kp.H;
     if (kp.ctrl_state) kp.ctrl_state += (size_t)r0 * kp.ctrl_stride;
+    if (kp.part_recs) kp.part_recs += (size_t)r0 * kp.tail_nb * kp.blk_rec_stride;
+    if (kp.tail_cnt) kp.tail_cnt += (size_t)r0 * tail_cnt_stride();
+    if (kp.tail_keys) kp.tail_keys += (size_t)r0 * 2 * kp.n_local;
     kp.robot_base += (uint32_t)r0;
 }
 
@@ -1026,15 +1060,16 @@ static int run_tick(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *ou
             cudaGraph_t g = nullptr;
             CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, h->stream);
-            void *args[] = {(void *)&kp};
-            cudaLaunchKernel((const void *)h->tick_fn, grid, dim3(h->threads), args, h->smem_bytes, h->stream);
+            const int lrc = launch(h, h->tick_fn, kp, grid);       // one kernel, or the (tick, tail) pair of a large launch
+            h->launches -= (h->tail_nb > 0 ? 2 : 1);               // counted per replay below
             cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream);
             CK(cudaStreamEndCapture(h->stream, &g));
+            if (lrc) { if (g) cudaGraphDestroy(g); return lrc; }
             CK(cudaGraphInstantiate(&h->graph_exec, g, 0));
             CK(cudaGraphDestroy(g));
         }
         CK(cudaGraphLaunch(h->graph_exec, h->stream));
-        h->launches++;
+        h->launches += (h->tail_nb > 0 ? 2 : 1);
     } else {
         if (!mapped) CK(cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, h->stream));
         rc = launch(h, h->tick_fn, kp, grid);

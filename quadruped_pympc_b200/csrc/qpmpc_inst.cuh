@@ -9,9 +9,9 @@ typedef void (*KernelFn)(const KParams);
 }
 
 extern "C" {
-void qp_inst_tick_zero(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
-void qp_inst_tick_linear(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
-void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3]);
+void qp_inst_tick_zero(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3], qp::KernelFn tail[2][3]);
+void qp_inst_tick_linear(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3], qp::KernelFn tail[2][3]);
+void qp_inst_tick_cubic(qp::KernelFn tick[2][3], qp::KernelFn fin[2][3], qp::KernelFn tick_h[2][3], qp::KernelFn tail[2][3]);
 void qp_inst_quad_zero(qp::KernelFn quad[2][3]);
 void qp_inst_quad_linear(qp::KernelFn quad[2][3]);
 void qp_inst_quad_cubic(qp::KernelFn quad[2][3]);

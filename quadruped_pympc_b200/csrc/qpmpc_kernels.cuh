@@ -100,6 +100,12 @@ struct KParams {
     int peer_rank;                          //      NVLink, waits for the peers' records and finishes in the same launch
     float *peer_mbox[MAX_PEERS];            // mailbox base of every rank (own entry = local memory): see peer_exchange
     unsigned long long *phase_ns;           // debug (qpmpc_debug_phase_times): %globaltimer at phase boundaries, or NULL
+    // ---- two-stage launches (qpmpc_tail.cuh): the tick kernel stops after its block records, tail_kernel finishes ----
+    int defer_tail;                         // 1: no last-block stage in the tick kernel
+    int tail_nb;                            // blocks per robot of tail_kernel
+    float *part_recs;                       // [R][tail_nb][blk_rec_stride] partial records
+    unsigned int *tail_cnt;                 // [R][8] {selected, candidates, ticket, ...}, zero between launches
+    unsigned long long *tail_keys;          // [R][2][n_local] selected / candidate keys of the elite selection (CEM only)
 };
 
 static_assert(sizeof(KParams) <= 4096, "KParams must fit the classic 4 KB kernel-parameter space");

@@ -692,6 +692,7 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
         for (int p = t; p < kp.P; p += TB) rec[REC_V + p] = s.v[p];
+    if (kp.defer_tail) return;                          // large launches: tail_kernel (qpmpc_tail.cuh) finishes the tick
     // release / acquire around the ticket by ONE thread between two block barriers (the shape of cooperative groups'
     // grid sync): the barrier orders the block's record stores before thread 0's fence, which is cumulative; the last
     // block's readers are ordered after thread 0's second fence by the second barrier.  128 membars per block -> 1.

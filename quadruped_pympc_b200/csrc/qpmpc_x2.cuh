@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
     if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
         for (int p = t; p < kp.P; p += XTB) rec[REC_V + p] = s.v[p];
+    if (kp.defer_tail) return;                          // large launches: tail_kernel (qpmpc_tail.cuh) finishes the tick
     // release / acquire around the ticket by ONE thread between two block barriers (see tick_body)
     __syncthreads();
     if (t == 0) {

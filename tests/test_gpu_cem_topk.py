@@ -54,10 +54,11 @@ def test_elites_are_the_stable_argsort_of_the_costs(built, N, adaptive, elite_k,
 
 @pytest.mark.parametrize('lanes', LANES)
 @pytest.mark.parametrize('adaptive', [False, True])
-def test_heavy_ties_take_the_exact_slow_path(built, adaptive, lanes):
+@pytest.mark.parametrize('N', [6000, 40000])
+def test_heavy_ties_take_the_exact_slow_path(built, adaptive, lanes, N):
     """All-zero Q: every fixed-gait cost is exactly 0 and the adaptive ones take three values (A:500), so the threshold
-    bin overflows the shared-memory candidate list and the selection must still be the stable argsort."""
-    N = 6000
+    bin overflows the shared-memory candidate list and the selection must still be the stable argsort.  N = 40 000 runs
+    the two-stage launch (tick kernel + multi-block tail kernel, csrc/qpmpc_tail.cuh)."""
     cfg = qp.SamplerConfig.for_robot('go2', sampling_method='cem_mppi', control_parametrization='zero_order',
                                      num_parallel_computations=N, optimize_step_freq=adaptive, lanes_per_sample=lanes,
                                      q_diag=(0.0,) * 12)
@@ -85,3 +86,32 @@ def test_moderate_ties_are_resolved_by_index_digits(built, lanes):
     costs, elite, best = _tick_cem(ctrl, sc, sigma)
     assert len(elite) == 200
     np.testing.assert_array_equal(elite, np.argsort(costs, kind='stable')[:200])
+
+
+@pytest.mark.parametrize('lanes', LANES)
+@pytest.mark.parametrize('N,robot,adaptive', [(30000, 'go2', False), (50000, 'hyqreal1', True), (120000, 'aliengo', True)])
+def test_two_stage_launch_elites_and_merge(built, N, robot, adaptive, lanes):
+    """From 192 block records on the reduction tail runs as a second, multi-block kernel (csrc/qpmpc_tail.cuh): slices of
+    the costs filtered against the histogram threshold by 32 blocks, two-level record merge.  The elite set must still be
+    the exact stable argsort of the device's costs, tick after tick (counters and histogram come back clean), and the
+    MPPI update must equal the one-level merge of a host replay of the weights."""
+    cfg = qp.SamplerConfig.for_robot(robot, sampling_method='cem_mppi', control_parametrization='cubic_spline',
+                                     num_parallel_computations=N, optimize_step_freq=adaptive, lanes_per_sample=lanes)
+    ctrl = qp.Sampling_MPC(cfg)
+    sc = synthetic.scenario(robot, 'pace', seed=4)
+    P = ctrl.num_control_parameters
+    sigma = np.full(P, 3.0, np.float32)
+    k = 200 if adaptive else 10
+    for _ in range(3):
+        ctrl.with_newkey()
+        key = ctrl.master_key.copy()
+        out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], np.zeros(P, np.float32), key,
+                                          sigma, sc['phase_signal'], sc['nominal_step_freq'], 1)
+        costs = np.asarray(out[6])
+        want = np.argsort(costs, kind='stable')[:k]
+        np.testing.assert_array_equal(ctrl.last_elite_indices, want)
+        assert ctrl.last_best_index == want[0]
+        noise = ctrl.generate_noise(key, sigma)
+        w = np.exp(-(costs.astype(np.float64) - float(costs.min())))
+        best = (w[:, None] * noise.astype(np.float64)).sum(0) / w.sum()
+        np.testing.assert_allclose(out[3], best, rtol=1e-4, atol=2e-5)

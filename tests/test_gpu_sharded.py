@@ -142,3 +142,31 @@ def test_peer_attach_refuses_two_shards_on_one_gpu(built):
     blobs = [a.peer_export(), b.peer_export()]
     with pytest.raises(_lib.QpmpcError, match='same GPU'):
         a.peer_attach(blobs)
+
+
+@pytest.mark.parametrize('method', ['mppi', 'cem_mppi'])
+def test_sharded_two_stage_shards_equal_unsharded(built, method):
+    """Shards large enough for the two-stage launch (tick kernel + multi-block tail kernel): the shard records, and the
+    tick finished from them, must match the unsharded controller (itself two-stage at this size)."""
+    N, world = 120000, 3
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=N, sampling_method=method)
+    sc = synthetic.scenario('go2', 'trot', seed=6)
+    key = np.array([42, 3], np.uint32)
+    best0 = np.zeros(96, np.float32)
+    sig = (np.full(96, 3.0, np.float32),) if method == 'cem_mppi' else ()
+    ctrl = qp.Sampling_MPC(cfg)
+    whole = ctrl.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, *sig,
+                                 sc['phase_signal'], 1.4, 0)
+    costs = np.asarray(whole[6])
+    shards = [qp.Sampling_MPC(cfg, shard_rank=r, shard_world=world) for r in range(world)]
+    recs = [s.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sigma=sig[0] if sig else None)
+            for s in shards]
+    out = shards[0].shard_finish(recs)
+    assert shards[0].last_best_index == int(np.argmin(costs)) == ctrl.last_best_index
+    np.testing.assert_allclose(out[4], whole[4], rtol=1e-6)
+    np.testing.assert_allclose(out[3], whole[3], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(out[0], whole[0], rtol=1e-4, atol=2e-4)
+    if method == 'cem_mppi':
+        np.testing.assert_array_equal(shards[0].last_elite_indices, np.argsort(costs, kind='stable')[:10])
+        np.testing.assert_array_equal(ctrl.last_elite_indices, shards[0].last_elite_indices)
+        np.testing.assert_allclose(out[7], whole[7], rtol=1e-4, atol=1e-6)
