@@ -86,8 +86,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     (host API + six kernel-instantiation units) are compiled in parallel, then linked into one shared library."""
     files = sorted(os.listdir(CSRC))
     srcs = [os.path.join(CSRC, f) for f in files]
-    newest = max(os.path.getmtime(p) for p in srcs + [HEADER])
+    newest = max(os.path.getmtime(p) for p in srcs + [HEADER] if not p.endswith('qpfast.c'))
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= newest:
+        if not os.path.exists(fast_path()) or os.path.getmtime(fast_path()) < os.path.getmtime(os.path.join(CSRC, 'qpfast.c')):
+            build_fast()
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
     obj_dir = os.path.join(LIB_DIR, 'obj')
@@ -109,7 +111,46 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise subprocess.CalledProcessError(p.returncode, f'nvcc -c {u}')
         objs.append(obj)
     subprocess.check_call(['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', LIB_PATH] + objs + ['-ldl'])
+    build_fast()
     return LIB_PATH
+
+
+def fast_path():
+    import sysconfig
+    return os.path.join(LIB_DIR, '_qpfast' + (sysconfig.get_config_var('EXT_SUFFIX') or '.so'))
+
+
+def build_fast() -> str:
+    """gcc-compile the CPython binding of the tick call (csrc/qpfast.c: marshalling only, links libqpmpc_b200.so)."""
+    import sysconfig
+    import numpy
+    out = fast_path()
+    subprocess.check_call(['gcc', '-O2', '-fPIC', '-shared', '-I' + sysconfig.get_paths()['include'], '-I' + numpy.get_include(),
+                           os.path.join(CSRC, 'qpfast.c'), '-o', out, '-L' + LIB_DIR, '-lqpmpc_b200', '-Wl,-rpath,$ORIGIN'])
+    return out
+
+
+_fast = None
+
+
+def load_fast():
+    """The CPython binding of qpmpc_tick / qpmpc_step (lib/_qpfast*.so), or None when it has not been built for this
+    interpreter (the ctypes path is then used: same C ABI, ~8 us more Python per tick)."""
+    global _fast
+    if _fast is None:
+        _fast = False
+        p = fast_path()
+        if os.path.exists(p):
+            load()                                          # libqpmpc_b200.so first (the module links against it)
+            import importlib.util
+            spec = importlib.util.spec_from_file_location('_qpfast', p)
+            try:
+                mod = importlib.util.module_from_spec(spec)
+                spec.loader.exec_module(mod)
+                _fast = mod
+            except ImportError:
+                _fast = False
+    return _fast or None
 
 
 _lib = None

@@ -62,6 +62,7 @@ class SamplerConfig:
     use_graph: bool = True
     elite_k: int = 0                 # 0 = reference default (10 / 200)
     lanes_per_sample: int = 0        # kernel variant: 0 = auto, 1 = sample per thread, 2 = two samples per thread (packed FP32), 4 = four lanes per sample, 14 = 1 + noise helpers
+    fast_binding: bool = True        # tick through the CPython binding (csrc/qpfast.c) when built; False: ctypes (same C ABI)
     q_diag: Sequence[float] = Q_DIAG_DEFAULT
 
     def __post_init__(self):

@@ -72,3 +72,90 @@ static PyObject *f32_array(const float *src, npy_intp n) {
     if (a) memcpy(PyArray_DATA((PyArrayObject *)a), src, (size_t)n * sizeof(float));
     return a;
 }
+
+static PyObject *qpfast_tick(PyObject *self, PyObject *const *args, Py_ssize_t nargs) {
+    (void)self;
+    if (nargs != 17) { PyErr_SetString(PyExc_TypeError, "tick() takes 17 positional arguments"); return NULL; }
+    qpmpc_handle *h = (qpmpc_handle *)PyLong_AsVoidPtr(args[0]);
+    const long mode = PyLong_AsLong(args[1]);
+    const long P = PyLong_AsLong(args[14]), H = PyLong_AsLong(args[15]), elite_k = PyLong_AsLong(args[16]);
+    if (PyErr_Occurred()) return NULL;
+    if (!h || P < 1 || P > QPF_MAX_P || H < 1 || H > QPMPC_MAX_HORIZON || elite_k < 0 || elite_k > QPMPC_MAX_ELITE) {
+        PyErr_SetString(PyExc_ValueError, "bad handle / sizes");
+        return NULL;
+    }
+    float state[24], reference[24], contact[4 * QPMPC_MAX_HORIZON], best[QPF_MAX_P], sigma[QPF_MAX_P], timing[4];
+    float best_out[QPF_MAX_P], sigma_out[QPF_MAX_P];
+    int32_t elite[QPMPC_MAX_ELITE];
+    qpmpc_tick_in in;
+    qpmpc_tick_out out;
+    memset(&in, 0, sizeof(in));
+    memset(&out, 0, sizeof(out));
+    if (to_f32(args[2], state, 24) || to_f32(args[3], reference, 24) || contact_to_f32(args[4], contact, (int)H)) return NULL;
+    in.state = state; in.reference = reference; in.contact_sequence = contact; in.contact_ld = (int32_t)H;
+    if (args[5] != Py_None) { if (to_f32(args[5], best, P)) return NULL; in.best = best; }
+    in.key[0] = (uint32_t)PyLong_AsUnsignedLongMask(args[6]);
+    in.key[1] = (uint32_t)PyLong_AsUnsignedLongMask(args[7]);
+    const int have_sigma = args[8] != Py_None;
+    if (have_sigma) {
+        if (PyFloat_Check(args[8]) || PyLong_Check(args[8])) {           /* with_newsigma(cfg scalar), I:128-129 */
+            const float sv = (float)PyFloat_AsDouble(args[8]);
+            for (long p = 0; p < P; ++p) sigma[p] = sv;
+        } else if (PyArray_Check(args[8]) && PyArray_SIZE((PyArrayObject *)args[8]) == 1) {
+            PyObject *f = PyNumber_Float(args[8]);
+            if (!f) return NULL;
+            const float sv = (float)PyFloat_AsDouble(f);
+            Py_DECREF(f);
+            for (long p = 0; p < P; ++p) sigma[p] = sv;
+        } else if (to_f32(args[8], sigma, P)) return NULL;
+        in.sigma = sigma;
+    }
+    if (args[9] != Py_None) { if (to_f32(args[9], timing, 4)) return NULL; in.phase_signal = timing; }
+    in.nominal_step_freq = args[10] == Py_None ? 0.0f : (float)PyFloat_AsDouble(args[10]);
+    in.optimize_swing = args[11] == Py_None ? 0 : (int32_t)PyLong_AsLong(args[11]);
+    const long iterations = PyLong_AsLong(args[12]);
+    const float sigma0 = (float)PyFloat_AsDouble(args[13]);
+    if (PyErr_Occurred()) return NULL;
+    out.best = best_out; out.sigma_new = sigma_out; out.elite_indices = elite;
+    int rc;
+    Py_BEGIN_ALLOW_THREADS
+    switch (mode) {
+        case 0: rc = qpmpc_tick(h, &in, &out); break;
+        case 1: rc = qpmpc_tick_sharded(h, &in, &out); break;
+        case 2: rc = qpmpc_tick_iterations(h, &in, (int32_t)iterations, &out); break;
+        case 3: rc = qpmpc_step(h, &in, (int32_t)iterations, sigma0, &out); break;
+        default: rc = QPF_ERR_ARG;
+    }
+    Py_END_ALLOW_THREADS
+    if (rc != 0) return PyLong_FromLong(rc);
+    PyObject *g = f32_array(out.grfs, 12), *pr = f32_array(out.predicted_state, 24), *b = f32_array(best_out, P);
+    PyObject *sg = NULL, *el = NULL;
+    if (elite_k > 0) {
+        sg = f32_array(sigma_out, P);
+        npy_intp n = out.num_elite < 0 ? 0 : out.num_elite;
+        el = PyArray_SimpleNew(1, &n, NPY_INT32);
+        if (el) memcpy(PyArray_DATA((PyArrayObject *)el), elite, (size_t)n * sizeof(int32_t));
+    } else {
+        sg = Py_None; Py_INCREF(sg);
+        el = Py_None; Py_INCREF(el);
+    }
+    if (!g || !pr || !b || !sg || !el) { Py_XDECREF(g); Py_XDECREF(pr); Py_XDECREF(b); Py_XDECREF(sg); Py_XDECREF(el); return NULL; }
+    PyObject *res = PyTuple_New(8);
+    if (!res) return NULL;
+    PyTuple_SET_ITEM(res, 0, g); PyTuple_SET_ITEM(res, 1, pr); PyTuple_SET_ITEM(res, 2, b);
+    PyTuple_SET_ITEM(res, 3, PyFloat_FromDouble((double)out.best_cost));
+    PyTuple_SET_ITEM(res, 4, PyFloat_FromDouble((double)out.best_freq));
+    PyTuple_SET_ITEM(res, 5, PyLong_FromLong((long)out.best_index));
+    PyTuple_SET_ITEM(res, 6, sg); PyTuple_SET_ITEM(res, 7, el);
+    return res;
+}
+
+static PyMethodDef qpfast_methods[] = {
+    {"tick", (PyCFunction)(void (*)(void))qpfast_tick, METH_FASTCALL, "one MPC tick through the C ABI (see module docstring)"},
+    {NULL, NULL, 0, NULL}};
+static struct PyModuleDef qpfast_module = {PyModuleDef_HEAD_INIT, "_qpfast",
+                                           "CPython binding of qpmpc_tick / qpmpc_step (marshalling only)", -1, qpfast_methods};
+PyMODINIT_FUNC PyInit__qpfast(void) {
+    import_array();
+    return PyModule_Create(&qpfast_module);
+}

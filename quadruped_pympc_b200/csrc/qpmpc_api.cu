@@ -256,7 +256,7 @@ struct qpmpc_handle {
     qpmpc_config cfg;
     KParams kp;                       // template: constants + device pointers for MODE_TICK
     int R, N, H, P, n_local;
-    size_t smem_bytes, finish_smem_bytes;
+    size_t smem_bytes, finish_smem_bytes, tail_smem_bytes = 0;
     cudaStream_t stream = nullptr;
     float *d_in = nullptr, *d_out = nullptr, *d_costs = nullptr, *d_blk = nullptr, *d_send = nullptr, *d_recv = nullptr;
     float *d_noise = nullptr, *d_freqs = nullptr, *d_flush = nullptr, *d_sigma = nullptr;
@@ -540,7 +540,9 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
-    CKH(cudaFuncSetAttribute((const void *)h->tail_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
+    h->tail_smem_bytes = smem_floats(kp.in_stride, h->P, TAIL_TB, TAIL_TB + 1) * sizeof(float);
+    if (h->tail_smem_bytes > 227 * 1024) h->tail_nb = 0;                  // (P > 200 knots: keep the fused path)
+    CKH(cudaFuncSetAttribute((const void *)h->tail_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->tail_smem_bytes));
     CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
@@ -563,13 +565,18 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     if (h->tail_nb > 0) {
         CKH(cudaMalloc((void **)&h->d_part, R * (size_t)h->tail_nb * kp.blk_rec_stride * sizeof(float)));
         CKH(cudaMalloc((void **)&h->d_tail_cnt, R * tail_cnt_stride() * sizeof(unsigned int)));
-        CKH(cudaMemset(h->d_tail_cnt, 0, R * tail_cnt_stride() * sizeof(unsigned int)));
+        {
+            std::vector<unsigned int> init(R * tail_cnt_stride(), 0u);
+            for (size_t r = 0; r < R; ++r) init[r * tail_cnt_stride() + 4] = 0xffffffffu;     // empty bin window
+            CKH(cudaMemcpy(h->d_tail_cnt, init.data(), init.size() * sizeof(unsigned int), cudaMemcpyHostToDevice));
+        }
         if (cfg->method == QPMPC_CEM_MPPI) CKH(cudaMalloc((void **)&h->d_tail_keys, R * 2 * (size_t)h->n_local * sizeof(unsigned long long)));
         kp.tail_nb = h->tail_nb; kp.part_recs = h->d_part; kp.tail_cnt = h->d_tail_cnt; kp.tail_keys = h->d_tail_keys;
     }
     if (cfg->method == QPMPC_CEM_MPPI) {       // per-robot cost histogram: zero between ticks (the last block re-zeroes it)
-        CKH(cudaMalloc((void **)&h->d_cem_hist, R * (size_t)CEM_BINS * sizeof(unsigned int)));
-        CKH(cudaMemset(h->d_cem_hist, 0, R * (size_t)CEM_BINS * sizeof(unsigned int)));
+        const size_t bins = h->tail_nb > 0 ? CEM_BINS_FINE : CEM_BINS;      // two-stage launches use the fine histogram
+        CKH(cudaMalloc((void **)&h->d_cem_hist, R * bins * sizeof(unsigned int)));
+        CKH(cudaMemset(h->d_cem_hist, 0, R * bins * sizeof(unsigned int)));
     }
     CKH(cudaMemset(h->d_in, 0, R * kp.in_stride * sizeof(float)));
     CKH(cudaMemset(h->d_out, 0, R * kp.out_stride * sizeof(float)));
@@ -681,7 +688,16 @@ static int launch(qpmpc_handle *h, KernelFn fn, const KParams &kp, dim3 grid, cu
         k2.defer_tail = 1;
         void *args[] = {(void *)&k2};
         CK(cudaLaunchKernel((const void *)fn, grid, dim3(h->threads), args, h->smem_bytes, st));
-        CK(cudaLaunchKernel((const void *)h->tail_fn, dim3(h->tail_nb, grid.y), dim3(TB), args, h->finish_smem_bytes, st));
+        // programmatic dependent launch: the tail's blocks are scheduled while the tick kernel drains (it triggers at its
+        // start) and wait in griddepcontrol.wait for its completion -- hides the ~5 us launch latency between the two
+        cudaLaunchConfig_t lc;
+        memset(&lc, 0, sizeof(lc));
+        lc.gridDim = dim3(h->tail_nb, grid.y); lc.blockDim = dim3(TAIL_TB); lc.dynamicSmemBytes = h->tail_smem_bytes; lc.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        lc.attrs = attr; lc.numAttrs = 1;
+        CK(cudaLaunchKernelExC(&lc, (const void *)h->tail_fn, args));
         h->launches += 2;
         return QPMPC_OK;
     }
@@ -940,7 +956,7 @@ static void offset_robots(KParams &kp, int r0) {
     kp.blk_recs += (size_t)r0 * kp.nblk * kp.blk_rec_stride;
     kp.shard_send += (size_t)r0 * kp.shard_rec_stride;
     kp.counters += r0;
-    if (kp.cem_hist) kp.cem_hist += (size_t)r0 * CEM_BINS;
+    if (kp.cem_hist) kp.cem_hist += (size_t)r0 * (kp.tail_nb > 0 ? CEM_BINS_FINE : CEM_BINS);
     if (kp.contact_dev) kp.contact_dev += (size_t)r0 * 4 * kp.H;
     if (kp.ctrl_state) kp.ctrl_state += (size_t)r0 * kp.ctrl_stride;
     if (kp.part_recs) kp.part_recs += (size_t)r0 * kp.tail_nb * kp.blk_rec_stride;

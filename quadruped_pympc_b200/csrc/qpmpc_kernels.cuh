@@ -712,10 +712,29 @@ static __device__ void block_topk(const float *costs, int n, int idx_base, int k
 // Falls back to block_topk (8 passes over global memory) if even the 24-bit prefix leaves more than CEM_CAND candidates
 // (thousands of bit-identical costs).  Same contract as block_topk; s_keys: >= MAX_ELITE + CEM_CAND u64.
 // ------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cem_count_cost(unsigned int *g_hist, float cost) {
-    const unsigned int bin = __float_as_uint(cost) >> CEM_SHIFT;
-    const unsigned int peers = __match_any_sync(__activemask(), bin);           // one RED per distinct bin per warp
-    if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(g_hist + bin, (unsigned int)__popc(peers));
+// Two-stage launches (kp.defer_tail, qpmpc_tail.cuh) count into a FINE histogram instead: cost bits >> CEM_SHIFT_FINE
+// (65 536 bins, 128 per octave: narrow cost distributions -- HyQReal at 50k samples sits inside one octave -- put a few
+// hundred keys into the threshold bin instead of half of all samples) and track the occupied bin window
+// (tail_cnt[4] = min bin, [5] = max bin) so that the tail scans a few hundred bins, not 65 536.
+constexpr int CEM_SHIFT_FINE = 16;
+constexpr int CEM_BINS_FINE = 65536;
+__device__ __forceinline__ void cem_count_cost(const KParams &kp, int r, float cost) {
+    const unsigned int active = __activemask();
+    if (!kp.defer_tail) {
+        const unsigned int bin = __float_as_uint(cost) >> CEM_SHIFT;
+        const unsigned int peers = __match_any_sync(active, bin);               // one RED per distinct bin per warp
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(kp.cem_hist + (size_t)r * CEM_BINS + bin, (unsigned int)__popc(peers));
+        return;
+    }
+    const unsigned int bin = __float_as_uint(cost) >> CEM_SHIFT_FINE;
+    const unsigned int peers = __match_any_sync(active, bin);
+    if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(kp.cem_hist + (size_t)r * CEM_BINS_FINE + bin, (unsigned int)__popc(peers));
+    const unsigned int lo = __reduce_min_sync(active, bin), hi = __reduce_max_sync(active, bin);
+    if ((threadIdx.x & 31) == __ffs(active) - 1) {
+        unsigned int *cnt = kp.tail_cnt + (size_t)r * 8;
+        atomicMin(cnt + 4, lo);
+        atomicMax(cnt + 5, hi);
+    }
 }
 
 // Block-wide search of the bin where the running count reaches `need`; bins[] are read through LOAD(i), i in

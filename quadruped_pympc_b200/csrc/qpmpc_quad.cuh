@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
     const int leg = t & 3, slot = t >> 2;
     __shared__ int s_last;
     if (blk == 0) phase_mark(kp, 0);
+    if (kp.defer_tail) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // see tick_body
     stage_inputs<QTB>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
     const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             if (leg == 0) {
                 kp.costs[(size_t)r * kp.n_local + local] = cost;
                 if (METHOD == CEM_MPPI && kp.mode == MODE_TICK)  // first radix level of the elite selection (block_topk_hist)
-                    cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, cost);
+                    cem_count_cost(kp, r, cost);
             }
         }
         if (blk == 0 && it == 0) phase_mark(kp, 3);

@@ -7,8 +7,8 @@
 // records and 54 us selecting elites while 147 SMs idled, and at 1 M samples 1 184 records.  From QPMPC_TAIL_MIN_BLOCKS
 // records on, the tick kernel stops after its block records (kp.defer_tail) and this kernel finishes the tick with
 // kp.tail_nb blocks per robot:
-//   1. (CEM) every block finds the threshold bin of the 4096-bin cost histogram the rollouts filled -- the same bin in
-//      every block -- and filters ITS SLICE of the costs: keys below the bin go to the `selected` list, keys inside it to
+//   1. (CEM) every block finds the threshold bin of the fine cost histogram the rollouts filled (65 536 bins of the cost
+//      bits >> 16, only the occupied window is scanned) -- the same bin in every block -- and filters ITS SLICE of the costs: keys below the bin go to the `selected` list, keys inside it to
 //      the `candidate` list (global memory, atomic append; the order inside the lists does not matter, the result is the
 //      exact sorted top-k);
 //   2. every block merges ITS SLICE of the block records into one partial record (online softmax, fixed order);
@@ -24,6 +24,7 @@
 namespace qp {
 
 constexpr int TAIL_MAX_NB = 32;
+constexpr int TAIL_TB = 256;      // threads per tail block: the CEM elite refit stages up to 256 noise rows in one pass
 
 // exact `need` smallest of `n` 64-bit keys (cost bits << 32 | index) that all share the cost prefix above bit
 // (32 + pshift): appended to s_keys[*s_count ...].  keys in global memory.  s_cand: CEM_CAND u64, s_hist: 4096 u32
@@ -160,15 +161,47 @@ static __device__ void refine_candidates(const unsigned long long *keys, unsigne
     __syncthreads();
 }
 
+// Block-wide search of the bin where the running count over `nb` consecutive bins of a GLOBAL histogram reaches `need`:
+// s_misc[0..2] = (bin offset | 0xffffffff, count below, count inside).  s_warp: >= NT/32 u32.
+template <int NT>
+static __device__ void find_bin_window(const unsigned int *bins, int nb, unsigned int need, unsigned int *s_warp, unsigned int *s_misc) {
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    const int per = (nb + NT - 1) / NT, lo = t * per, hi = lo + per < nb ? lo + per : nb;
+    unsigned int mysum = 0u;
+    for (int i = lo; i < hi; ++i) mysum += __ldcg(bins + i);
+    unsigned int incl = mysum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    __syncthreads();
+    if (lane == 31) s_warp[wid] = incl;
+    if (t == 0) s_misc[0] = 0xffffffffu;
+    __syncthreads();
+    unsigned int excl = incl - mysum;
+    for (int w = 0; w < wid; ++w) excl += s_warp[w];
+    if (excl < need && excl + mysum >= need) {                                    // exactly one thread
+        unsigned int acc = excl;
+        for (int i = lo; i < hi; ++i) {
+            const unsigned int c = __ldcg(bins + i);
+            if (acc + c >= need) { s_misc[0] = (unsigned int)i; s_misc[1] = acc; s_misc[2] = c; break; }
+            acc += c;
+        }
+    }
+    __syncthreads();
+}
+
 // per-robot scratch of the tail kernel (global memory): counters [8] = {selected, candidates, ticket, -, ...}, then the
 // two key lists (n_local u64 each; the selected list holds < k keys, the candidate list at most n_local)
 __host__ __device__ inline size_t tail_cnt_stride() { return 8; }
 
-// grid = (tail_nb, R), block = TB.
+// grid = (tail_nb, R), block = TAIL_TB.
 template <int PARAM, bool ADAPTIVE, int METHOD>
-__global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KParams kp) {
+__global__ void __launch_bounds__(TAIL_TB, 1) tail_kernel(const __grid_constant__ KParams kp) {
     extern __shared__ __align__(16) float smem_raw[];
-    const Smem s(smem_raw, kp);
+    constexpr int TB = TAIL_TB;                          // (shadows the tick kernels' block size inside this kernel)
+    const Smem s(smem_raw, kp, TB);
     const int t = threadIdx.x, blk = blockIdx.x, r = blockIdx.y, NB = gridDim.x;
     __shared__ int s_last;
     unsigned int *cnt = kp.tail_cnt + (size_t)r * tail_cnt_stride();
@@ -177,24 +210,31 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
     unsigned int *hist = reinterpret_cast<unsigned int *>(s.tile + 2 * SCRATCH_KEYS);
     unsigned int *misc = hist + 256;
     const int k = kp.elite_k < kp.n_local ? kp.elite_k : kp.n_local;
+    // Launched as a programmatic dependent of the tick kernel.  The tick's inputs (packet, carried controller state, device
+    // contact tables) are not written by the tick kernel, so every block stages them NOW, while that kernel is still
+    // running; then wait until its grid has completed and its stores are visible.
+    stage_inputs<TB>(kp, r, s);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (blk == 0) phase_mark(kp, 8);
-    // ---- 1. CEM: threshold bin of the cost histogram, then this block's slice of the costs ----
-    if (METHOD == CEM_MPPI) {
-        unsigned int *g_hist = kp.cem_hist + (size_t)r * CEM_BINS;
-        uint4 *s4 = reinterpret_cast<uint4 *>(keys);
-        for (int i = t; i < CEM_BINS / 4; i += TB) s4[i] = __ldcg(reinterpret_cast<const uint4 *>(g_hist) + i);
+    // ---- 1. CEM: threshold bin of the (fine, windowed) cost histogram, then this block's slice of the costs ----
+    // CEM: the first half of the blocks filters cost slices, the second half merges block records -- the two jobs overlap
+    const int NBF = (METHOD == CEM_MPPI && NB >= 2) ? NB / 2 : 0;         // filter blocks
+    const int NBM = NB - NBF;                                             // merge blocks = partial records
+    unsigned int win_lo = 0u, win_hi = 0u;
+    if (METHOD == CEM_MPPI) { win_lo = __ldcg(&cnt[4]); win_hi = __ldcg(&cnt[5]); }          // occupied bins (cem_count_cost)
+    if (METHOD == CEM_MPPI && (blk < NBF || NB < 2)) {
+        const int FB = NB < 2 ? 1 : NBF;
+        const unsigned int *g_hist = kp.cem_hist + (size_t)r * CEM_BINS_FINE;
+        find_bin_window<TB>(g_hist + win_lo, (int)(win_hi - win_lo + 1u), (unsigned int)k, hist, misc);
+        const unsigned int thr = misc[0] == 0xffffffffu ? 0xffffffffu : win_lo + misc[0];
         __syncthreads();
-        const unsigned int *s_h1 = reinterpret_cast<const unsigned int *>(keys);
-        cem_find_bin<TB>([&](int i) { return s_h1[i]; }, (unsigned int)k, hist, misc);
-        const unsigned int thr = misc[0];
-        __syncthreads();
-        const int per = (((kp.n_local + NB - 1) / NB) + 3) & ~3;           // 16-byte aligned slices
+        const int per = (((kp.n_local + FB - 1) / FB) + 3) & ~3;           // 16-byte aligned slices
         const int lo = blk * per, n_slice = kp.n_local - lo < per ? kp.n_local - lo : per;
         const float *costs = kp.costs + (size_t)r * kp.n_local;
         if (n_slice > 0 && thr != 0xffffffffu) {
             const int idx_base = kp.sample_base + lo;
             cem_for_each_cost<TB>(costs + lo, n_slice, [&](unsigned int cb, int i) {
-                const unsigned int b = cb >> CEM_SHIFT;
+                const unsigned int b = cb >> CEM_SHIFT_FINE;
                 if (b <= thr) {
                     const unsigned long long key = ((unsigned long long)cb << 32) | (unsigned int)(idx_base + i);
                     if (b < thr) sel[atomicAdd(&cnt[0], 1u)] = key;
@@ -202,12 +242,14 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
                 }
             });
         }
+        if (blk == 0) phase_mark(kp, 4);
     }
     // ---- 2. this block's slice of the block records -> one partial record ----
-    {
-        const int per = (kp.nblk + NB - 1) / NB;
-        const int lo = blk * per, n = kp.nblk - lo < per ? kp.nblk - lo : per;
-        float *part = kp.part_recs + ((size_t)r * NB + blk) * kp.blk_rec_stride;
+    if (blk >= NBF || NB < 2) {
+        const int mb = NB < 2 ? 0 : blk - NBF;
+        const int per = (kp.nblk + NBM - 1) / NBM;
+        const int lo = mb * per, n = kp.nblk - lo < per ? kp.nblk - lo : per;
+        float *part = kp.part_recs + ((size_t)r * NB + mb) * kp.blk_rec_stride;
         float M = CUDART_INF_F, S = 0.0f;
         int IDX = 0x7fffffff;
         __syncthreads();
@@ -215,6 +257,7 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
         if (t == 0) { part[REC_M] = M; part[REC_IDX] = __int_as_float(IDX); part[REC_S] = S; part[REC_PAD] = 0.0f; }
         if (METHOD != RANDOM_SAMPLING)
             for (int p = t; p < kp.P; p += TB) part[REC_V + p] = n > 0 ? s.v[p] : 0.0f;
+        if (mb == 0) phase_mark(kp, 5);
     }
     __syncthreads();
     if (t == 0) {
@@ -226,9 +269,9 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
     __syncthreads();
     if (!s_last) return;
     // ---- 3. last block: the tick's inputs, the merged record, the exact elite set, then as the fused kernel ----
-    stage_inputs<TB>(kp, r, s);
+    phase_mark(kp, 1);
     float M, S; int IDX;
-    merge_records<METHOD, TB>(kp.part_recs + (size_t)r * NB * kp.blk_rec_stride, NB, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
+    merge_records<METHOD, TB>(kp.part_recs + (size_t)r * NB * kp.blk_rec_stride, NB < 2 ? 1 : NBM, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
     float *rec = kp.shard_send + (size_t)r * kp.shard_rec_stride;
     if (t == 0) { rec[REC_M] = M; rec[REC_IDX] = __int_as_float(IDX); rec[REC_S] = S; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
@@ -236,12 +279,12 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
     if (METHOD == CEM_MPPI) {
         __syncthreads();
         const unsigned int nsel = __ldcg(&cnt[0]), m = __ldcg(&cnt[1]);
-        unsigned int *g_hist = kp.cem_hist + (size_t)r * CEM_BINS;
-        for (int i = t; i < CEM_BINS / 4; i += TB) reinterpret_cast<uint4 *>(g_hist)[i] = make_uint4(0u, 0u, 0u, 0u);   // for the next tick
+        unsigned int *g_hist = kp.cem_hist + (size_t)r * CEM_BINS_FINE;
+        for (unsigned int i = win_lo + t; i <= win_hi; i += TB) g_hist[i] = 0u;                    // clean for the next tick
         if (t == 0) misc[3] = 0u;
         __syncthreads();
         if (m > 0 && (int)nsel < k)
-            refine_candidates<TB>(cand, m, k - (int)nsel, CEM_SHIFT, keys, &misc[3], keys + MAX_ELITE,
+            refine_candidates<TB>(cand, m, k - (int)nsel, CEM_SHIFT_FINE, keys, &misc[3], keys + MAX_ELITE,
                                   reinterpret_cast<unsigned int *>(keys), hist, misc);
         __syncthreads();
         for (unsigned int i = t; i < nsel; i += TB) { const unsigned int slot = atomicAdd(&misc[3], 1u); if (slot < MAX_ELITE) keys[slot] = __ldcg(sel + i); }
@@ -258,7 +301,7 @@ __global__ void __launch_bounds__(TB, 4) tail_kernel(const __grid_constant__ KPa
         }
         __syncthreads();
     }
-    if (t == 0) { cnt[0] = 0u; cnt[1] = 0u; cnt[2] = 0u; }
+    if (t == 0) { cnt[0] = 0u; cnt[1] = 0u; cnt[2] = 0u; cnt[4] = 0xffffffffu; cnt[5] = 0u; }
     phase_mark(kp, 9);
     after_shard_reduce<PARAM, ADAPTIVE, METHOD, TB>(kp, r, s, M, IDX, S);
     phase_mark(kp, 11);

@@ -349,6 +349,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         } else if (kp.carry_best) {
             const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + IN_TICK] = __uint_as_float(tick + 1u);
         }
+        phase_mark(kp, 6);
     }
     if (METHOD != CEM_MPPI) return;
     // ---- CEM elite refit ----
@@ -370,7 +371,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         keys[j] = key;
     }
     __syncthreads();
-    bitonic_sort_u64<NT>(keys, npow);
+    if (world > 1) bitonic_sort_u64<NT>(keys, npow);       // one shard: its record already holds the keys in ascending order
     const int k = K < kp.N ? K : kp.N;                     // argsort(costs)[:k]
     int *out_elite = reinterpret_cast<int *>(out + kp.off_out_elite);
     for (int j = t; j < K; j += TB) {
@@ -380,6 +381,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     }
     if (t == 0) out[OUT_NELITE] = __int_as_float(k);
     __syncthreads();                                       // the tile scratch (keys) is reused for the elite rows below
+    phase_mark(kp, 7);
     // Per-knot mean / M2 over the elites, chunked by TB rows with an exact two-pass inside a chunk and Chan's
     // pairwise update between chunks (same result as the two-pass diag(cov) of S:1077 to rounding).
     float n_acc = 0.0f;
@@ -409,6 +411,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
             }
         }
         __syncthreads();
+        if (kp.defer_tail && base == 0) phase_mark(kp, 2);
 #pragma unroll
         for (int j = 0; j < MAXV; ++j) {
             const int p = t + j * TB;
@@ -429,6 +432,7 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
             }
         }
         n_acc += (float)cnt;
+        if (kp.defer_tail && base == 0) phase_mark(kp, 3);
     }
 #pragma unroll
     for (int j = 0; j < MAXV; ++j) {
@@ -598,6 +602,9 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     const int t = NH > 1 ? (int)(threadIdx.x & (TB - 1)) : (int)threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
     const int hlp = NH > 1 ? (int)(threadIdx.x / TB) : 0;
     if (blk == 0) phase_mark(kp, 0);
+    // two-stage launch: let the dependent tail_kernel be scheduled now (programmatic dependent launch); its blocks wait in
+    // griddepcontrol.wait until this whole grid has completed and flushed, so only the launch latency overlaps
+    if (kp.defer_tail) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     stage_inputs<TB * NH>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
     const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
@@ -656,7 +663,7 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
             }
             kp.costs[(size_t)r * kp.n_local + local] = cost;
             if (METHOD == CEM_MPPI && kp.mode == MODE_TICK)      // first radix level of the elite selection (block_topk_hist)
-                cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, cost);
+                cem_count_cost(kp, r, cost);
         }
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }
         if (blk == 0 && it == 0) phase_mark(kp, 3);

@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
     const int t = threadIdx.x, blk = blockIdx.x, r = blockIdx.y;
     __shared__ int s_last;
     if (blk == 0) phase_mark(kp, 0);
+    if (kp.defer_tail) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // see tick_body
     stage_inputs<XTB>(kp, r, s);
     if (blk == 0) phase_mark(kp, 1);
     const uint32_t seed = __float_as_uint(s.in[IN_SEED]), robot = kp.robot_base + (uint32_t)r, tick = __float_as_uint(s.in[IN_TICK]);
@@ -119,8 +120,8 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
             cdst[0] = c0;
             if (act1) cdst[1] = c1;
             if (METHOD == CEM_MPPI && kp.mode == MODE_TICK) {    // first radix level of the elite selection (block_topk_hist)
-                cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, c0);
-                if (act1) cem_count_cost(kp.cem_hist + (size_t)r * CEM_BINS, c1);
+                cem_count_cost(kp, r, c0);
+                if (act1) cem_count_cost(kp, r, c1);
             }
         }
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }

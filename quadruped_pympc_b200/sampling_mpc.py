@@ -215,6 +215,8 @@ class Sampling_MPC:
         h = C.c_void_p()
         _lib.check(lib.qpmpc_create(C.byref(c), C.byref(h)))
         self._handle, self._pid = h, os.getpid()
+        self._hptr = int(h.value)
+        self._fast = _lib.load_fast() if self.cfg.fast_binding else None   # CPython binding of the tick call (csrc/qpfast.c)
         self._stateful = False                                  # a new handle starts without a device record
         self._shift_set = 0.0
         self._n_local = lib.qpmpc_num_local_samples(h)
@@ -488,11 +490,16 @@ class Sampling_MPC:
             best = _f32(self.best_control_parameters, (self.num_control_parameters,))
             _lib.check(lib.qpmpc_step_reset(h, key, _fp(best), None))
             self._stateful = True
-        b.fill(st, rf, contact_sequence, 0.0, (0, 0), None, pgg_phase_signal, pgg_step_freq, optimize_swing, None, None,
-               self.horizon)
         self._tick_serial += 1
-        _lib.check(lib.qpmpc_step(h, C.byref(b.cin), n, float(self.cfg.sigma_cem_mppi), C.byref(b.cout)))
-        out = self._unpack(b)
+        if self._fast is not None and contact_sequence is not None:
+            out = self._fast_result(self._fast.tick(self._hptr, 3, st, rf, contact_sequence, None, 0, 0, None, pgg_phase_signal,
+                                                    pgg_step_freq, optimize_swing, n, float(self.cfg.sigma_cem_mppi),
+                                                    self.num_control_parameters, self.horizon, self.elite_k))
+        else:
+            b.fill(st, rf, contact_sequence, 0.0, (0, 0), None, pgg_phase_signal, pgg_step_freq, optimize_swing, None, None,
+                   self.horizon)
+            _lib.check(lib.qpmpc_step(h, C.byref(b.cin), n, float(self.cfg.sigma_cem_mppi), C.byref(b.cout)))
+            out = self._unpack(b)
         self.best_control_parameters = out[3]
         self.master_key = np.array([self.master_key[0], (int(self.master_key[1]) + n) & 0xFFFFFFFF], dtype=np.uint32)
         if self._cem:
@@ -530,6 +537,14 @@ class Sampling_MPC:
     def _tick(self, state, reference, contact_sequence, best, key, sigma, timing, nominal, optimize_swing, noise,
               step_freqs, iterations=1):
         h = self._ensure()
+        if noise is None and step_freqs is None and self._fast is not None:
+            # the real-time path: csrc/qpfast.c reads the caller's arrays in place and calls the same C-ABI entry point
+            k0, k1 = key.tolist() if isinstance(key, np.ndarray) else key
+            mode = 2 if iterations != 1 else (0 if self._shard[1] == 1 else 1)
+            res = self._fast.tick(self._hptr, mode, state, reference, contact_sequence, best, k0, k1, sigma, timing, nominal,
+                                  optimize_swing, iterations, 0.0, self.num_control_parameters, self.horizon, self.elite_k)
+            self._tick_serial += 1
+            return self._fast_result(res)
         lib = _lib.load()
         b = self._buf
         if noise is not None:
@@ -550,6 +565,16 @@ class Sampling_MPC:
         else:
             _lib.check(lib.qpmpc_tick_sharded(h, C.byref(b.cin), C.byref(b.cout)))
         return self._unpack(b)
+
+    def _fast_result(self, res):
+        if type(res) is int:
+            _lib.check(res)
+        grfs, pred, best, best_cost, best_freq, self.last_best_index, sigma_new, elite = res
+        out = (grfs, _ZERO_FOOTHOLDS, pred, best, np.float32(best_cost), best_freq, LazyCosts(self))
+        if self._cem:
+            self.last_elite_indices = elite.astype(np.int64)
+            out = out + (sigma_new,)
+        return out
 
     def _unpack(self, b):
         o = b.cout

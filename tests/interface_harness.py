@@ -182,7 +182,8 @@ def run_case(name, robot, gait, overrides):
     real = _lib.load()
     rec = RecordingLib(real)
     _lib._lib = rec                                   # what _lib.load() hands out from now on
-    try:
+    fast_saved, _lib._fast = _lib._fast, False        # the ctypes binding is the one a stand-in library can observe (the
+    try:                                              # CPython binding of the same call is compared with it on the GPU)
         mod = patched_interface_module()
         iface = mod.SRBDControllerInterface()
         assert type(iface.controller) is qp.Sampling_MPC, 'the patched interface did not construct the B200 controller'
@@ -194,5 +195,6 @@ def run_case(name, robot, gait, overrides):
         iface.controller.close()
     finally:
         _lib._lib = real
+        _lib._fast = fast_saved
         mp.pop(key, None)
     return rec, outs, inputs

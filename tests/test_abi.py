@@ -121,3 +121,12 @@ def test_robot_ids_must_fit_the_philox_counter_field(built):
     h = C.c_void_p()
     assert lib.qpmpc_create(C.byref(c), C.byref(h)) == _lib.ERR_INVALID
     assert b'2^23' in lib.qpmpc_last_error()
+
+
+def test_cpython_binding_builds_and_refuses_to_tick_without_a_device(built):
+    """csrc/qpfast.c (the CPython binding of the tick call) is built next to the library; without a handle it raises
+    instead of computing anything."""
+    fast = _lib.load_fast()
+    assert fast is not None and hasattr(fast, 'tick')
+    with pytest.raises(ValueError):
+        fast.tick(0, 0, np.zeros(24), np.zeros(24), np.ones((4, 12)), np.zeros(96, np.float32), 42, 1, None, None, 1.4, 0, 1, 0.0, 96, 12, 0)

@@ -261,3 +261,37 @@ def test_replay_of_the_reference_interface_trace_matches_the_oracle(built, case)
         if cem:
             got['new_sigma_cem_mppi'], got['elite_indices'] = out[7], ctrl.last_elite_indices
         assert_tick_parity(ref, got, cem=cem, noise=noise)
+
+
+@pytest.mark.parametrize('method,adaptive', [('mppi', False), ('cem_mppi', False), ('random_sampling', True), ('cem_mppi', True)])
+def test_cpython_binding_equals_ctypes_binding(built, method, adaptive):
+    """The tick call has two bindings of the SAME C-ABI entry point: ctypes (quadruped_pympc_b200/_lib.py) and the CPython
+    module csrc/qpfast.c (marshalling only, ~8 us less Python per tick).  Same inputs -- float64 arrays, a (4, 2H)
+    contact table, a non-contiguous state, scalar sigma -- must give the same bits."""
+    from quadruped_pympc_b200 import _lib
+    assert _lib.load_fast() is not None, 'lib/_qpfast*.so has not been built'
+    sc = synthetic.scenario('go2', 'trot', seed=5)
+    outs = []
+    for fast in (True, False):
+        cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='cubic_spline',
+                                         num_parallel_computations=1500, optimize_step_freq=adaptive, fast_binding=fast)
+        ctrl = qp.Sampling_MPC(cfg)
+        state = np.asfortranarray(np.stack([sc['state'], sc['state']], axis=1))[:, 0]          # strided float64 view
+        cs = np.concatenate([sc['contact_sequence'], np.ones((4, 12))], axis=1)                  # (4, 2H), I: FULL_STANCE shape
+        best = np.linspace(-1, 1, 96).astype(np.float32)
+        res = []
+        for it in range(3):
+            ctrl.with_newkey()
+            args = ((3 if it == 0 else sigma),) if method == 'cem_mppi' else ()
+            args = args + ((sc['phase_signal'], sc['nominal_step_freq'], 1) if (adaptive or method != 'cem_mppi') else ())
+            out = ctrl.jitted_compute_control(state, sc['reference'], cs, best, ctrl.master_key, *args)
+            best = out[3]
+            if method == 'cem_mppi':
+                sigma = out[7]
+            res.append([np.asarray(x) for x in out] + [ctrl.last_best_index] +
+                       ([ctrl.last_elite_indices] if method == 'cem_mppi' else []))
+        assert (ctrl._fast is not None) == fast
+        outs.append(res)
+    for a, b in zip(*outs):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)

@@ -50,7 +50,7 @@ def resident(method='mppi', param='cubic_spline', N=10000, R=1, lanes=0, adaptiv
 def fmt_phases(ph):
     b0 = ph[0]
     names = {1: 'staged', 2: 'noise', 3: 'rollout', 4: 'reduced', 5: 'published', 8: 'last:ticket', 9: 'last:merged',
-             10: 'last:best', 11: 'last:done', 12: 'm:argmin', 13: 'm:chunk0sum', 14: 'm:vdone', 15: 'last:publish'}
+             6: 'f:tail', 7: 'f:elites', 10: 'last:best', 11: 'last:done', 12: 'm:argmin', 13: 'm:chunk0sum', 14: 'm:vdone', 15: 'last:publish'}
     return ' '.join(f'{names[k]}@{(ph[k] - b0) / 1e3:.1f}' for k in sorted(names) if ph[k] > 0)
 
 
