@@ -273,6 +273,11 @@ int qpmpc_shard_peer_loopback(qpmpc_handle *h);
 int qpmpc_shard_peer_inject(qpmpc_handle *h, int rank, const float *host_rec);
 /* peer exchange if attached (one launch), else partial + ncclAllGather + finish */
 int qpmpc_tick_sharded(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *out);
+/* How long the in-kernel exchange waits for the peers' records before the tick fails with QPMPC_ERR_NCCL (default 2 s). */
+int qpmpc_shard_peer_timeout(qpmpc_handle *h, double seconds);
+/* Debug: with enable != 0 every following peer-exchange tick records this GPU's %globaltimer (ns) when its last block
+ * starts pushing the shard record (out[0]) and when it has taken all peers' records (out[1]); out = the last tick's pair. */
+int qpmpc_debug_peer_wait(qpmpc_handle *h, int32_t enable, uint64_t out[2]);
 
 /* ---- device-resident benchmarking helpers (inputs already in HBM; CUDA-event timing on the handle's stream) */
 /* Upload one packet per robot and keep it resident; subsequent qpmpc_bench_resident calls replay it. */

@@ -73,7 +73,7 @@ EXPORTS = [
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
     'qpmpc_shard_peer_export', 'qpmpc_shard_peer_attach', 'qpmpc_shard_peer_loopback', 'qpmpc_shard_peer_inject',
-    'qpmpc_tick_sharded', 'qpmpc_upload_resident', 'qpmpc_bench_resident', 'qpmpc_bench_resident_wall', 'qpmpc_fetch_resident_out',
+    'qpmpc_tick_sharded', 'qpmpc_debug_peer_wait', 'qpmpc_shard_peer_timeout', 'qpmpc_upload_resident', 'qpmpc_bench_resident', 'qpmpc_bench_resident_wall', 'qpmpc_fetch_resident_out',
     'qpmpc_kernel_launch_count', 'qpmpc_measure_fp32_peak', 'qpmpc_debug_phase_times',
 ]
 
@@ -214,6 +214,8 @@ def load():
     lib.qpmpc_shard_peer_loopback.argtypes = [H]
     lib.qpmpc_shard_peer_inject.argtypes = [H, C.c_int, _FP]
     lib.qpmpc_tick_sharded.argtypes = [H, C.POINTER(QpmpcTickIn), C.POINTER(QpmpcTickOut)]
+    lib.qpmpc_debug_peer_wait.argtypes = [H, C.c_int32, C.POINTER(C.c_uint64)]
+    lib.qpmpc_shard_peer_timeout.argtypes = [H, C.c_double]
     lib.qpmpc_upload_resident.argtypes = [H, C.POINTER(QpmpcTickIn)]
     lib.qpmpc_bench_resident.argtypes = [H, C.c_int, C.c_int, _FP]
     lib.qpmpc_bench_resident_wall.argtypes = [H, C.c_int, C.c_int, _FP, _FP]

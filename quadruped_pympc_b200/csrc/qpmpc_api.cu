@@ -303,6 +303,9 @@ struct qpmpc_handle {
     float *peer_mbox[MAX_PEERS] = {}; // every rank's mailbox as seen from this device
     bool peer_ipc[MAX_PEERS] = {};    // opened with cudaIpcOpenMemHandle (to be closed)
     bool peer_attached = false;
+    bool peer_timing = false;         // qpmpc_debug_peer_wait
+    unsigned long long peer_timeout_ns = 2000000000ull;   // qpmpc_shard_peer_timeout
+    uint64_t peer_wait_ns[2] = {0, 0};
 };
 
 static size_t round4(size_t x) { return (x + 3) & ~(size_t)3; }
@@ -1649,10 +1652,10 @@ extern "C" int qpmpc_shard_peer_inject(qpmpc_handle *h, int rank, const float *h
     if (seq == 0u) seq = 1u;
     const unsigned int par = seq & 1u;
     const size_t slot = (size_t)(par * W + rank) * R;
-    CK(cudaMemcpy(h->d_mbox + slot * stride, host_rec, (size_t)R * stride * sizeof(float), cudaMemcpyHostToDevice));
-    std::vector<unsigned int> stamps((size_t)R, seq);
-    unsigned int *d_stamps = reinterpret_cast<unsigned int *>(h->d_mbox + peer_mbox_rec_floats(W, R, stride)) + slot;
-    CK(cudaMemcpy(d_stamps, stamps.data(), (size_t)R * sizeof(unsigned int), cudaMemcpyHostToDevice));
+    // the peer's record as the {value, seq} units its kernel would have stored (qpmpc_tick.cuh peer_exchange)
+    std::vector<uint32_t> units((size_t)R * stride * 2);
+    for (size_t k = 0; k < (size_t)R * stride; ++k) { units[2 * k] = f2u(host_rec[k]); units[2 * k + 1] = seq; }
+    CK(cudaMemcpy(reinterpret_cast<uint32_t *>(h->d_mbox) + slot * stride * 2, units.data(), units.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     return QPMPC_OK;
 }
 
@@ -1662,8 +1665,13 @@ static int tick_peer(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *o
     KParams kp = h->kp;
     kp.fused_finish = 0;
     kp.peer_world = h->cfg.shard_world; kp.peer_rank = h->cfg.shard_rank;
+    kp.peer_timeout_ns = h->peer_timeout_ns;
     memcpy(kp.peer_mbox, h->peer_mbox, sizeof(kp.peer_mbox));
     kp.seq = next_seq(h);                              // every rank ticks in lockstep: same stamp everywhere
+    if (h->peer_timing) {                              // qpmpc_debug_peer_wait: %globaltimer around the exchange (slots 6, 7)
+        if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 16 * sizeof(unsigned long long)));
+        kp.phase_ns = h->d_phase;
+    }
     int rc = stage_injection(h, in, R, kp);
     if (rc) return rc;
     const dim3 grid(kp.nblk, R);
@@ -1680,8 +1688,30 @@ static int tick_peer(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *o
         CK(cudaStreamSynchronize(h->stream));
         for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
     }
+    if (h->peer_timing) {
+        unsigned long long ph[16];
+        CK(cudaMemcpyAsync(ph, h->d_phase, sizeof(ph), cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        h->peer_wait_ns[0] = ph[6]; h->peer_wait_ns[1] = ph[7];
+    }
     for (int r = 0; r < R; ++r)
         if (out[r].best_index == -2) return fail(QPMPC_ERR_NCCL, "peer exchange timed out: a shard of this controller did not tick (robot %d)", r);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_shard_peer_timeout(qpmpc_handle *h, double seconds) {
+    if (!h || !(seconds > 0.0) || seconds > 3.5) return fail(QPMPC_ERR_INVALID, "timeout must be in (0, 3.5] s (the host-side deadline is 4 s)");
+    h->peer_timeout_ns = (unsigned long long)(seconds * 1e9);
+    return QPMPC_OK;
+}
+
+// Debug: %globaltimer (this GPU's clock, ns) when the last block of the last sharded tick started pushing its record and
+// when it had taken every peer's record: the difference is what the exchange costs this rank (transfer + waiting for
+// the slowest rank).
+extern "C" int qpmpc_debug_peer_wait(qpmpc_handle *h, int32_t enable, uint64_t out[2]) {
+    if (!h) return fail(QPMPC_ERR_INVALID, "NULL handle");
+    h->peer_timing = enable != 0;
+    if (out) { out[0] = h->peer_wait_ns[0]; out[1] = h->peer_wait_ns[1]; }
     return QPMPC_OK;
 }
 

@@ -99,6 +99,7 @@ struct KParams {
     int peer_world;                         // > 1: the last block pushes its shard record into every peer's mailbox over
     int peer_rank;                          //      NVLink, waits for the peers' records and finishes in the same launch
     float *peer_mbox[MAX_PEERS];            // mailbox base of every rank (own entry = local memory): see peer_exchange
+    unsigned long long peer_timeout_ns;     // the in-kernel wait for the peers' records gives up after this long
     unsigned long long *phase_ns;           // debug (qpmpc_debug_phase_times): %globaltimer at phase boundaries, or NULL
     // ---- two-stage launches (qpmpc_tail.cuh): the tick kernel stops after its block records, tail_kernel finishes ----
     int defer_tail;                         // 1: no last-block stage in the tick kernel

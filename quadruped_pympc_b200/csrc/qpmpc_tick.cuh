@@ -503,64 +503,65 @@ __device__ __forceinline__ int compact_weights(float w, int slot, bool owner, co
 
 // ------------------------------------------------------------------------------------------------------
 // Fused collective of a sample-sharded controller (one exchange step per tick): instead of a separate
-// all-gather launch, the last block of each shard stores its record straight into every peer GPU's mailbox (plain
-// stores to peer memory: NVLink / NVSwitch), publishes a sequence stamp with system-scope release, and spins
-// (acquire) until all `world` stamps of this tick have arrived in its own mailbox; finish() then merges the records
-// in rank order -- every rank ends the same launch with the same control.
-//   mailbox of one rank: recs [2 parity][world][R][shard_rec_stride] floats, then stamps [2][world][R] u32.
+// all-gather launch, the last block of each shard stores its record straight into every peer GPU's mailbox over NVLink /
+// NVSwitch and reads the peers' records from its own mailbox; finish() then merges the records in rank order -- every
+// rank ends the same launch with the same control.
+//   Wire format: self-validating 8-byte units {value, seq} (two per 16-byte store; an aligned 8-byte unit arrives whole
+//   over NVLink -- the scheme of NCCL's LL protocol, and of publish_to_host).  The receiver takes each unit as soon as its
+//   flag equals this tick's seq, so there is NO system-scope fence and NO separate stamp: the r1 version (record stores,
+//   __threadfence_system, st.release.sys stamps, ld.acquire.sys + nanosleep polling) cost ~16 us per tick.
+//   mailbox of one rank: units [2 parity][world][R][shard_rec_stride] of 8 bytes.
 //   Two parities: a rank that is one tick ahead writes the other half, and cannot get two ticks ahead because it
 //   needs this rank's record of the tick in between.
-// Returns false if a peer's stamp did not arrive within ~2 s (peer process gone): the caller reports it.
+// Returns false if a peer's record did not arrive within kp.peer_timeout_ns (default 2 s; peer process gone): the caller
+// reports it.
 // ------------------------------------------------------------------------------------------------------
-__host__ __device__ inline size_t peer_mbox_rec_floats(int world, int R, int stride) { return (size_t)2 * world * R * stride; }
-__host__ __device__ inline size_t peer_mbox_bytes(int world, int R, int stride) {
-    return peer_mbox_rec_floats(world, R, stride) * sizeof(float) + (size_t)2 * world * R * sizeof(unsigned int);
-}
-
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
+__host__ __device__ inline size_t peer_mbox_units(int world, int R, int stride) { return (size_t)2 * world * R * stride; }
+__host__ __device__ inline size_t peer_mbox_bytes(int world, int R, int stride) { return peer_mbox_units(world, R, stride) * 8; }
 
 template <int NT>
 __device__ bool peer_exchange(const KParams &kp, int r, const float *&recs, size_t &rec_stride) {
     const int W = kp.peer_world, R = gridDim.y, stride = kp.shard_rec_stride, t = threadIdx.x;
-    const unsigned int par = kp.seq & 1u;
+    const unsigned int par = kp.seq & 1u, seq = kp.seq;
     const size_t slot = ((size_t)(par * W + kp.peer_rank) * R + r);          // [parity][my rank][robot]
-    const float *mine = kp.shard_send + (size_t)r * stride;                   // written by this block in shard_reduce
+    const float2 *mine = reinterpret_cast<const float2 *>(kp.shard_send + (size_t)r * stride);   // written by this block
     __syncthreads();
-    // 1. push the record: float4 stores, one peer after the other per thread (W * stride/4 <= a few hundred stores)
-    const int n4 = stride >> 2;
-    for (int e = t; e < W * n4; e += NT) {
-        const int w = e / n4, k = e - w * n4;
-        reinterpret_cast<float4 *>(kp.peer_mbox[w] + slot * stride)[k] = reinterpret_cast<const float4 *>(mine)[k];
+    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[6] = ns; }
+    // 1. push the record to every rank (own mailbox included): 16-byte stores of two {value, seq} units
+    const int n2 = stride >> 1;                                               // stride is a multiple of 4
+    for (int e = t; e < W * n2; e += NT) {
+        const int w = e / n2, k = e - w * n2;
+        const float2 v = mine[k];
+        uint4 *dst = reinterpret_cast<uint4 *>(reinterpret_cast<uint2 *>(kp.peer_mbox[w]) + slot * stride) + k;
+        asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(__float_as_uint(v.x)), "r"(seq),
+                     "r"(__float_as_uint(v.y)), "r"(seq) : "memory");
     }
-    __threadfence_system();
-    __syncthreads();
-    // 2. stamp every peer's mailbox (release: the record is visible before the stamp)
-    const size_t stamps_off = peer_mbox_rec_floats(W, R, stride);
-    if (t < W) st_release_sys(reinterpret_cast<unsigned int *>(kp.peer_mbox[t] + stamps_off) + slot, kp.seq);
-    // 3. wait for the W stamps of this tick in the local mailbox
+    // 2. take the W records of this tick from the local mailbox, unit by unit, into the (local) receive buffer
     __shared__ int s_ok;
     if (t == 0) s_ok = 1;
     __syncthreads();
-    float *local = kp.peer_mbox[kp.peer_rank];
-    if (t < W) {
-        const unsigned int *st = reinterpret_cast<const unsigned int *>(local + stamps_off) + ((size_t)(par * W + t) * R + r);
-        unsigned long long t0, now;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        while (ld_acquire_sys(st) != kp.seq) {
-            __nanosleep(40);
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-            if (now - t0 > 2000000000ull) { s_ok = 0; break; }
+    const uint2 *local = reinterpret_cast<const uint2 *>(kp.peer_mbox[kp.peer_rank]);
+    float *recv = const_cast<float *>(kp.shard_recv);                         // [world][R][stride] floats
+    unsigned long long t0 = 0ull;
+    for (int e = t; e < W * stride; e += NT) {
+        const int w = e / stride, k = e - w * stride;
+        const uint2 *src = local + ((size_t)(par * W + w) * R + r) * stride + k;
+        unsigned int val, flag, spins = 0u;
+        for (;;) {
+            asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(val), "=r"(flag) : "l"(src) : "memory");
+            if (flag == seq) break;
+            if ((++spins & 1023u) == 0u) {                                    // bounded wait: a peer that never ticks
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0ull) t0 = now;
+                else if (now - t0 > kp.peer_timeout_ns) { s_ok = 0; break; }
+            }
         }
+        recv[((size_t)w * R + r) * stride + k] = __uint_as_float(val);
     }
     __syncthreads();
-    recs = local + ((size_t)par * W * R + r) * stride;
+    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[7] = ns; }
+    recs = recv + (size_t)r * stride;
     rec_stride = (size_t)R * stride;
     return s_ok != 0;
 }

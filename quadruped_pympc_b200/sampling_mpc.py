@@ -287,6 +287,18 @@ class Sampling_MPC:
         _lib.check(_lib.load().qpmpc_shard_peer_inject(self._ensure(), int(rank), _fp(_f32(record))))
         return self
 
+    def peer_timeout(self, seconds: float):
+        """How long the in-kernel exchange waits for the peers before a sharded tick fails with ERR_NCCL (default 2 s)."""
+        _lib.check(_lib.load().qpmpc_shard_peer_timeout(self._ensure(), float(seconds)))
+        return self
+
+    def debug_peer_wait(self, enable=True):
+        """(start, end) of the last peer exchange on this GPU's %globaltimer (ns); `enable` arms the recording for the
+        following sharded ticks (costs one extra synchronous copy per tick -- debugging only)."""
+        out = (C.c_uint64 * 2)()
+        _lib.check(_lib.load().qpmpc_debug_peer_wait(self._ensure(), int(bool(enable)), out))
+        return int(out[0]), int(out[1])
+
     def shard_partial(self, state, reference, contact_sequence, best, key, sigma=None, timing=None, nominal=None,
                       optimize_swing=None, noise=None, step_freqs=None) -> np.ndarray:
         """Rollouts + local reduction of this shard's slice; returns the shard record (floats) for a caller-side gather

@@ -7,6 +7,7 @@ import pytest
 
 import quadruped_pympc_b200 as qp
 from quadruped_pympc_b200 import synthetic
+from quadruped_pympc_b200 import _lib
 from helpers import make_pair, seeded_noise, seeded_freqs, assert_tick_parity
 
 pytestmark = pytest.mark.gpu
@@ -170,3 +171,29 @@ def test_sharded_two_stage_shards_equal_unsharded(built, method):
         np.testing.assert_array_equal(shards[0].last_elite_indices, np.argsort(costs, kind='stable')[:10])
         np.testing.assert_array_equal(ctrl.last_elite_indices, shards[0].last_elite_indices)
         np.testing.assert_allclose(out[7], whole[7], rtol=1e-4, atol=1e-6)
+
+
+def test_peer_exchange_times_out_when_a_rank_never_ticks(built):
+    """A shard whose peer never delivers its record (process gone) must not hang the controller: the in-kernel wait gives
+    up after its time-out (2 s by default; 0.1 s here), the tick returns QPMPC_ERR_NCCL, and the handle keeps working once
+    the peer is back."""
+    import time
+    cfg = qp.SamplerConfig.for_robot('go2', num_parallel_computations=2000, sampling_method='mppi')
+    sc = synthetic.scenario('go2', 'trot', seed=2)
+    best0 = np.zeros(96, np.float32)
+    me = qp.Sampling_MPC(cfg, shard_rank=0, shard_world=2).peer_loopback().peer_timeout(0.1)
+    peer = qp.Sampling_MPC(cfg, shard_rank=1, shard_world=2)
+    t0 = time.perf_counter()
+    with pytest.raises(_lib.QpmpcError) as e:
+        me.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, np.array([42, 1], np.uint32),
+                           sc['phase_signal'], 1.4, 0)
+    dt = time.perf_counter() - t0
+    assert e.value.code == _lib.ERR_NCCL and 0.09 < dt < 1.0, (e.value, dt)
+    # the peer comes back: its record for the next tick is delivered, the tick completes and matches the unsharded one
+    key = np.array([42, 2], np.uint32)
+    rec = peer.shard_partial(sc['state'], sc['reference'], sc['contact_sequence'], best0, key)
+    me.peer_inject(1, rec)
+    out = me.compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key, sc['phase_signal'], 1.4, 0)
+    whole = qp.Sampling_MPC(cfg).compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best0, key,
+                                                 sc['phase_signal'], 1.4, 0)
+    np.testing.assert_allclose(out[3], whole[3], rtol=1e-4, atol=1e-5)

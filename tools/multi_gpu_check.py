@@ -99,6 +99,25 @@ def main():
                     lat[i - 20] = t1 - t0
             tot = torch.tensor([lat.sum()], dtype=torch.float64, device='cuda')
             dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+            # ---- what the exchange itself costs: in-kernel wait of every rank (its own GPU clock), 60 ticks ----
+            waits = None
+            if exchange == 'peer':
+                ctrl.debug_peer_wait(True)
+                w = np.zeros(60)
+                for i in range(60):
+                    ctrl.with_newkey()
+                    o = tick(ctrl, sc, best, sigma)
+                    best = np.asarray(o[3], np.float32)
+                    a, b = ctrl.debug_peer_wait(True)
+                    w[i] = (b - a) * 1e-3
+                ctrl.debug_peer_wait(False)
+                wt = torch.tensor(w, dtype=torch.float64, device='cuda')
+                allw = [torch.zeros_like(wt) for _ in range(world)]
+                dist.all_gather(allw, wt)
+                allw = torch.stack(allw).cpu().numpy()                       # [rank][tick] us
+                # the rank that arrives LAST waits only for the transfer; the one that arrives first also waits for the skew
+                waits = {'exchange_us_p50': float(np.median(allw.min(axis=0))), 'skew_plus_exchange_us_p50': float(np.median(allw.max(axis=0))),
+                         'skew_plus_exchange_us_p99': float(np.percentile(allw.max(axis=0), 99))}
             if rank == 0:
                 line = {'what': 'sharded_controller', 'exchange': exchange, 'n_gpus': world, 'robot': robot, 'method': method,
                         'param': param, 'adaptive': adaptive, 'N': N, 'parity_ok': bool(ok), 'ranks_bit_identical': bool(identical),
@@ -106,6 +125,8 @@ def main():
                         'p99_us': float(np.percentile(lat, 99) * 1e6),
                         'rollout_steps_per_s': args.ticks * N * ctrl.horizon / float(tot.item()),
                         'elapsed_s': round(time.perf_counter() - t_start, 1)}
+                if waits:
+                    line['in_kernel_exchange'] = waits
                 print(json.dumps(line), flush=True)
                 lines.append(line)
             del ctrl                     # (NCCL-exchange handles release their communicator with ncclCommAbort)
