@@ -500,6 +500,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     memcpy(kp.I, cfg->inertia, sizeof(kp.I));
     inv3f(cfg->inertia, kp.Iinv);                                                   // M:56
     memcpy(kp.qd, cfg->q_diag, sizeof(kp.qd));
+    kp.q_xyyaw = (cfg->q_diag[0] != 0.f || cfg->q_diag[1] != 0.f || cfg->q_diag[8] != 0.f) ? 1 : 0;
     kp.mpc_dt = cfg->dts[H - 1];                                                    // A:179: pgg mpc_dt = self.dt
     kp.duty = cfg->pgg_duty_factor;
     memcpy(kp.sigma_rs, cfg->sigma_random_sampling, sizeof(kp.sigma_rs));
@@ -1669,7 +1670,7 @@ static int tick_peer(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *o
     memcpy(kp.peer_mbox, h->peer_mbox, sizeof(kp.peer_mbox));
     kp.seq = next_seq(h);                              // every rank ticks in lockstep: same stamp everywhere
     if (h->peer_timing) {                              // qpmpc_debug_peer_wait: %globaltimer around the exchange (slots 6, 7)
-        if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 16 * sizeof(unsigned long long)));
+        if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 24 * sizeof(unsigned long long)));
         kp.phase_ns = h->d_phase;
     }
     int rc = stage_injection(h, in, R, kp);
@@ -1689,10 +1690,10 @@ static int tick_peer(qpmpc_handle *h, const qpmpc_tick_in *in, qpmpc_tick_out *o
         for (int r = 0; r < R; ++r) unpack_one(h, r, h->h_out, &out[r]);
     }
     if (h->peer_timing) {
-        unsigned long long ph[16];
+        unsigned long long ph[24];
         CK(cudaMemcpyAsync(ph, h->d_phase, sizeof(ph), cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
-        h->peer_wait_ns[0] = ph[6]; h->peer_wait_ns[1] = ph[7];
+        h->peer_wait_ns[0] = ph[16]; h->peer_wait_ns[1] = ph[17];
     }
     for (int r = 0; r < R; ++r)
         if (out[r].best_index == -2) return fail(QPMPC_ERR_NCCL, "peer exchange timed out: a shard of this controller did not tick (robot %d)", r);
@@ -1794,7 +1795,7 @@ extern "C" int qpmpc_debug_phase_times(qpmpc_handle *h, uint64_t out[16]) {
     if (!h->resident_uploaded) return fail(QPMPC_ERR_STATE, "qpmpc_upload_resident has not been called");
     if (h->cfg.shard_world != 1) return fail(QPMPC_ERR_STATE, "needs an unsharded handle");
     CK(cudaSetDevice(h->cfg.device));
-    if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 16 * sizeof(unsigned long long)));
+    if (!h->d_phase) CK(cudaMalloc((void **)&h->d_phase, 24 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(h->d_phase, 0, 16 * sizeof(unsigned long long), h->stream));
     KParams kp = h->kp;
     kp.in = h->d_in; kp.out = h->d_out; kp.carry_best = 1; kp.phase_ns = h->d_phase;

@@ -60,6 +60,7 @@ struct KParams {
     float inv_m, mg, mu, fz_min, fz_max;
     float I[9], Iinv[9];
     float qd[12];
+    int q_xyyaw;                            // 1: q_diag weights x, y or yaw (the reference's Q does not)
     float mpc_dt, duty;
     float sigma_rs[3], sigma_mppi;
     float freq_avail[3];
@@ -160,8 +161,9 @@ __device__ __forceinline__ void box_muller16(uint32_t w, float c, float &z0, flo
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(c * l2));
     asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(th));
     asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(th));
-    z0 = r * cs;
-    z1 = r * sn;
+    const float2 z = __fmul2_rn(make_float2(cs, sn), make_float2(r, r));   // one FMUL2, r as the broadcast operand
+    z0 = z.x;
+    z1 = z.y;
 }
 constexpr float BM_C1 = -1.38629436f;         // -2 ln 2: unit-variance normals
 
@@ -348,9 +350,13 @@ __device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T F
     cost_term(c, b.wx, ref[9], kp.qd[9]);
     cost_term(c, b.wy, ref[10], kp.qd[10]);
     cost_term(c, b.wz, ref[11], kp.qd[11]);
-    cost_term(c, b.px, ref[0], kp.qd[0]);
-    cost_term(c, b.py, ref[1], kp.qd[1]);
-    cost_term(c, b.yaw, ref[8], kp.qd[8]);
+    // the reference's Q weights x, y and yaw with 0 (S:118-130): (e * 0) * e adds exactly nothing for every finite e, so
+    // the three terms sit behind ONE block-uniform branch (taken only for a non-default q_diag, which stays exact)
+    if (kp.q_xyyaw) {
+        cost_term(c, b.px, ref[0], kp.qd[0]);
+        cost_term(c, b.py, ref[1], kp.qd[1]);
+        cost_term(c, b.yaw, ref[8], kp.qd[8]);
+    }
     return c;
 }
 

@@ -526,7 +526,7 @@ __device__ bool peer_exchange(const KParams &kp, int r, const float *&recs, size
     const size_t slot = ((size_t)(par * W + kp.peer_rank) * R + r);          // [parity][my rank][robot]
     const float2 *mine = reinterpret_cast<const float2 *>(kp.shard_send + (size_t)r * stride);   // written by this block
     __syncthreads();
-    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[6] = ns; }
+    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[16] = ns; }
     // 1. push the record to every rank (own mailbox included): 16-byte stores of two {value, seq} units
     const int n2 = stride >> 1;                                               // stride is a multiple of 4
     for (int e = t; e < W * n2; e += NT) {
@@ -560,7 +560,7 @@ __device__ bool peer_exchange(const KParams &kp, int r, const float *&recs, size
         recv[((size_t)w * R + r) * stride + k] = __uint_as_float(val);
     }
     __syncthreads();
-    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[7] = ns; }
+    if (kp.phase_ns != nullptr && t == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[17] = ns; }
     recs = recv + (size_t)r * stride;
     rec_stride = (size_t)R * stride;
     return s_ok != 0;

@@ -21,7 +21,7 @@ FIXTURES = tick_fixtures()
 
 
 def test_fixtures_present():
-    assert len(FIXTURES) >= 22, f'golden fixtures missing under {GOLDEN_DIR} (run tools/make_golden.py)'
+    assert len(FIXTURES) >= 24, f'golden fixtures missing under {GOLDEN_DIR} (run tools/make_golden.py)'
 
 
 def _check(fx, got, exp, cost_rtol=COST_RTOL, vec_rtol=VEC_RTOL):

@@ -201,6 +201,12 @@ def main():
                       adaptive=False, N=N, seed=32, num_splines=3))
     cases.append(dict(tag='adaptive_random_sampling_cubic_noswing', robot='aliengo', gait='trot', method='random_sampling',
                       param='cubic_spline', adaptive=True, N=N, seed=33, optimize_swing=0))
+    # row a15 with optimize_swing = 0: mppi draws from step_freq_available regardless (A:835-838), cem_mppi collapses to the
+    # nominal frequency (A:994-1000)
+    cases.append(dict(tag='adaptive_mppi_linear_noswing', robot='go2', gait='pace', method='mppi', param='linear_spline',
+                      adaptive=True, N=N, seed=35, optimize_swing=0))
+    cases.append(dict(tag='adaptive_cem_mppi_cubic_noswing', robot='hyqreal1', gait='trot', method='cem_mppi', param='cubic_spline',
+                      adaptive=True, N=max(N, 260), seed=36, optimize_swing=0))
     cases.append(dict(tag='fixed_random_sampling_cubic_bigbest', robot='hyqreal1', gait='trot', method='random_sampling',
                       param='cubic_spline', adaptive=False, N=N, seed=34, best_scale=40.0))
     for c in cases:
