@@ -75,8 +75,9 @@ def bench_config(robots, world):
     return {'workload': workload_name(robots),
             'parallelism': f'robots partitioned over {world} GPU(s), no collective',
             'l2': 'flushed (256 MiB memset) before every timed tick, outside the timed span',
-            'timing': 'value = host wall clock per tick (launch call -> completion seen, L2 flush done before the clock '
-                      'starts), ranks released by a barrier, max over ranks; device = CUDA events around the kernel',
+            'timing': 'value = host wall clock per tick (launch call -> cudaStreamSynchronize returns, L2 flush done before '
+                      'the clock starts), ranks released by a barrier, max over ranks; device = a separate pass with CUDA '
+                      'events around the kernel',
             'noise': 'in-kernel Philox4x32-10 (GPU arm) / host Philox mirror (CPU arm)'}
 
 
@@ -286,8 +287,8 @@ def make_resident_handle(device, robots, robot_base, n_samples=None, lanes=None,
 
 
 def run_resident(h, steps, warmup, flush=1, wall=False):
-    """-> per-tick device times (ms) of `steps` resident ticks after `warmup` untimed ones, the launch count [and the
-    per-tick host wall times (ms) when wall=True]."""
+    """-> per-tick device times (ms) of `steps` resident ticks after `warmup` untimed ones, the launch count [and, when
+    wall=True, the per-tick host wall times (ms) of a SECOND pass of `steps` ticks timed without events]."""
     from quadruped_pympc_b200 import _lib
     lib = _lib.load()
     if warmup > 0:
@@ -296,10 +297,10 @@ def run_resident(h, steps, warmup, flush=1, wall=False):
     n0, n1 = C.c_uint64(0), C.c_uint64(0)
     _lib.check(lib.qpmpc_kernel_launch_count(h, C.byref(n0)))
     ms, wl = np.zeros(steps, np.float32), np.zeros(steps, np.float32)
-    if wall:
-        _lib.check(lib.qpmpc_bench_resident_wall(h, steps, flush, ms.ctypes.data_as(_lib._FP), wl.ctypes.data_as(_lib._FP)))
-    else:
-        _lib.check(lib.qpmpc_bench_resident(h, steps, flush, ms.ctypes.data_as(_lib._FP)))
+    _lib.check(lib.qpmpc_bench_resident(h, steps, flush, ms.ctypes.data_as(_lib._FP)))            # device: CUDA events
+    if wall:                                                                                          # host wall clock, no events
+        scratch = np.zeros(steps, np.float32)
+        _lib.check(lib.qpmpc_bench_resident_wall(h, steps, flush, scratch.ctypes.data_as(_lib._FP), wl.ctypes.data_as(_lib._FP)))
     _lib.check(lib.qpmpc_kernel_launch_count(h, C.byref(n1)))
     if wall:
         return ms.astype(np.float64), int(n1.value - n0.value), wl.astype(np.float64)

@@ -285,8 +285,9 @@ int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in);
 /* Runs `steps` resident ticks; ms[i] = device time of tick i (events around the kernel(s) only).  If
  * flush_l2 != 0 a buffer larger than L2 is rewritten before every timed tick (outside the events). */
 int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms);
-/* The same, plus wall_ms[i] = host wall clock of tick i from the launch call until the host sees its completion (the L2
- * flush has completed before the clock starts): includes launch latency and anything the ranks of one box contend for. */
+/* The same loop timed with the host wall clock instead of events: wall_ms[i] = launch call of tick i until
+ * cudaStreamSynchronize returns (the L2 flush has completed before the clock starts; ms[] is zeroed): includes launch
+ * latency and anything the ranks of one box contend for. */
 int qpmpc_bench_resident_wall(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms);
 int qpmpc_fetch_resident_out(qpmpc_handle *h, qpmpc_tick_out *out);  /* D2H of the last resident tick's outputs */
 int qpmpc_kernel_launch_count(const qpmpc_handle *h, uint64_t *count); /* kernels launched by this handle so far */

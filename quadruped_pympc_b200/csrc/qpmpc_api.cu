@@ -1749,8 +1749,8 @@ extern "C" int qpmpc_upload_resident(qpmpc_handle *h, const qpmpc_tick_in *in) {
 
 static int bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms);
 extern "C" int qpmpc_bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms) { return bench_resident(h, steps, flush_l2, ms, nullptr); }
-// the same, additionally with the HOST wall clock around every tick (launch call -> completion seen by the host; the L2
-// flush has finished before the clock starts): sees launch latency and whatever the ranks of one box contend for
+// the same loop timed with the HOST wall clock instead of events (launch call -> cudaStreamSynchronize returns; the L2 flush
+// has finished before the clock starts; ms[] is zeroed): sees launch latency and whatever the ranks of one box contend for
 extern "C" int qpmpc_bench_resident_wall(qpmpc_handle *h, int steps, int flush_l2, float *ms, float *wall_ms) {
     if (!wall_ms) return fail(QPMPC_ERR_INVALID, "bad argument");
     return bench_resident(h, steps, flush_l2, ms, wall_ms);
@@ -1768,14 +1768,21 @@ static int bench_resident(qpmpc_handle *h, int steps, int flush_l2, float *ms, f
     const dim3 grid(kp.nblk, h->R);
     for (int i = 0; i < steps; ++i) {
         if (flush_l2) CK(cudaMemsetAsync(h->d_flush, i & 0xff, flush_bytes, h->stream));
-        uint64_t t0 = 0;
-        if (wall_ms) { CK(cudaStreamSynchronize(h->stream)); t0 = mono_ns(); }
+        if (wall_ms) {                                       // host clock: launch call -> cudaStreamSynchronize returns (no events in
+            CK(cudaStreamSynchronize(h->stream));            // the way; the flush has completed before the clock starts)
+            const uint64_t t0 = mono_ns();
+            int rc = launch(h, h->tick_fn, kp, grid);
+            if (rc) return rc;
+            CK(cudaStreamSynchronize(h->stream));
+            wall_ms[i] = (float)(1e-6 * (double)(mono_ns() - t0));
+            ms[i] = 0.0f;
+            continue;
+        }
         CK(cudaEventRecord(h->ev0, h->stream));
         int rc = launch(h, h->tick_fn, kp, grid);
         if (rc) return rc;
         CK(cudaEventRecord(h->ev1, h->stream));
         CK(cudaEventSynchronize(h->ev1));
-        if (wall_ms) wall_ms[i] = (float)(1e-6 * (double)(mono_ns() - t0));
         CK(cudaEventElapsedTime(&ms[i], h->ev0, h->ev1));
     }
     return QPMPC_OK;

@@ -115,3 +115,28 @@ def test_two_stage_launch_elites_and_merge(built, N, robot, adaptive, lanes):
         w = np.exp(-(costs.astype(np.float64) - float(costs.min())))
         best = (w[:, None] * noise.astype(np.float64)).sum(0) / w.sum()
         np.testing.assert_allclose(out[3], best, rtol=1e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize('method', ['mppi', 'cem_mppi'])
+def test_two_stage_launch_inside_a_captured_graph(built, method):
+    """io_mode='memcpy' replays a captured CUDA graph (H2D, kernels, D2H).  At 30 000 samples the graph holds the (tick,
+    tail) pair with its programmatic dependency; the replayed ticks must equal the direct-I/O handle bit for bit."""
+    outs = []
+    sc = synthetic.scenario('go2', 'trot', seed=8)
+    for io in ('direct', 'memcpy'):
+        cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='cubic_spline',
+                                         num_parallel_computations=30000, io_mode=io)
+        ctrl = qp.Sampling_MPC(cfg)
+        P = ctrl.num_control_parameters
+        best, res = np.zeros(P, np.float32), []
+        for _ in range(3):
+            ctrl.with_newkey()
+            args = (np.full(P, 3.0, np.float32),) if method == 'cem_mppi' else ()
+            out = ctrl.jitted_compute_control(sc['state'], sc['reference'], sc['contact_sequence'], best, ctrl.master_key,
+                                              *args, sc['phase_signal'], sc['nominal_step_freq'], 0)
+            best = out[3]
+            res.append([np.asarray(x) for x in out] + [ctrl.last_best_index])
+        outs.append(res)
+    for a, b in zip(*outs):
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)

@@ -67,7 +67,7 @@ def test_sharded_philox_equals_unsharded(built):
     np.testing.assert_allclose(out[0], whole[0], rtol=1e-4, atol=1e-4)
 
 
-@pytest.mark.parametrize('lanes', [1, 4, 14])
+@pytest.mark.parametrize('lanes', [1, 4, 14, 2])
 @pytest.mark.parametrize('method,adaptive,world', [('random_sampling', False, 2), ('mppi', False, 3), ('cem_mppi', False, 8),
                                                    ('mppi', True, 2), ('cem_mppi', True, 4)])
 def test_fused_peer_exchange_loopback(built, method, adaptive, world, lanes):
