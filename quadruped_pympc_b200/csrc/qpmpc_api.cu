@@ -567,7 +567,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_sigma, (size_t)h->P * sizeof(float)));
     CKH(cudaMemset(h->d_counters, 0, R * sizeof(unsigned int)));
     if (h->tail_nb > 0) {
-        CKH(cudaMalloc((void **)&h->d_part, R * (size_t)h->tail_nb * kp.blk_rec_stride * sizeof(float)));
+        CKH(cudaMalloc((void **)&h->d_part, R * (size_t)TAIL_NPART * kp.blk_rec_stride * sizeof(float)));
         CKH(cudaMalloc((void **)&h->d_tail_cnt, R * tail_cnt_stride() * sizeof(unsigned int)));
         {
             std::vector<unsigned int> init(R * tail_cnt_stride(), 0u);
@@ -963,7 +963,7 @@ static void offset_robots(KParams &kp, int r0) {
     if (kp.cem_hist) kp.cem_hist += (size_t)r0 * (kp.tail_nb > 0 ? CEM_BINS_FINE : CEM_BINS);
     if (kp.contact_dev) kp.contact_dev += (size_t)r0 * 4 * kp.H;
     if (kp.ctrl_state) kp.ctrl_state += (size_t)r0 * kp.ctrl_stride;
-    if (kp.part_recs) kp.part_recs += (size_t)r0 * kp.tail_nb * kp.blk_rec_stride;
+    if (kp.part_recs) kp.part_recs += (size_t)r0 * TAIL_NPART * kp.blk_rec_stride;
     if (kp.tail_cnt) kp.tail_cnt += (size_t)r0 * tail_cnt_stride();
     if (kp.tail_keys) kp.tail_keys += (size_t)r0 * 2 * kp.n_local;
     kp.robot_base += (uint32_t)r0;

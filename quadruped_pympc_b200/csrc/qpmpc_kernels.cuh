@@ -105,7 +105,7 @@ struct KParams {
     // ---- two-stage launches (qpmpc_tail.cuh): the tick kernel stops after its block records, tail_kernel finishes ----
     int defer_tail;                         // 1: no last-block stage in the tick kernel
     int tail_nb;                            // blocks per robot of tail_kernel
-    float *part_recs;                       // [R][tail_nb][blk_rec_stride] partial records
+    float *part_recs;                       // [R][TAIL_NPART][blk_rec_stride] partial records
     unsigned int *tail_cnt;                 // [R][8] {selected, candidates, ticket, ...}, zero between launches
     unsigned long long *tail_keys;          // [R][2][n_local] selected / candidate keys of the elite selection (CEM only)
 };

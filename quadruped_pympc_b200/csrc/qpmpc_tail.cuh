@@ -11,7 +11,8 @@
 //      bits >> 16, only the occupied window is scanned) -- the same bin in every block -- and filters ITS SLICE of the costs: keys below the bin go to the `selected` list, keys inside it to
 //      the `candidate` list (global memory, atomic append; the order inside the lists does not matter, the result is the
 //      exact sorted top-k);
-//   2. every block merges ITS SLICE of the block records into one partial record (online softmax, fixed order);
+//   2. the block records are merged into TAIL_NPART = 32 partial records (online softmax, fixed slices and order -- the
+//      same whatever the number of blocks, so results do not depend on how robots are grouped into launches);
 //   3. last-block-done: the last block merges the tail_nb partial records, refines the candidates to the exact k
 //      smallest (cost, index) keys (shared-memory radix select; a second 12-bit histogram level first when the threshold
 //      bin is crowded), and continues exactly like the fused kernel's last block (shard record, peer exchange or finish,
@@ -24,6 +25,7 @@
 namespace qp {
 
 constexpr int TAIL_MAX_NB = 32;
+constexpr int TAIL_NPART = 32;    // partial records per robot: FIXED, so that the merge order does not depend on how many blocks share the work
 constexpr int TAIL_TB = 256;      // threads per tail block: the CEM elite refit stages up to 256 noise rows in one pass
 
 // exact `need` smallest of `n` 64-bit keys (cost bits << 32 | index) that all share the cost prefix above bit
@@ -247,16 +249,18 @@ __global__ void __launch_bounds__(TAIL_TB, 1) tail_kernel(const __grid_constant_
     // ---- 2. this block's slice of the block records -> one partial record ----
     if (blk >= NBF || NB < 2) {
         const int mb = NB < 2 ? 0 : blk - NBF;
-        const int per = (kp.nblk + NBM - 1) / NBM;
-        const int lo = mb * per, n = kp.nblk - lo < per ? kp.nblk - lo : per;
-        float *part = kp.part_recs + ((size_t)r * NB + mb) * kp.blk_rec_stride;
-        float M = CUDART_INF_F, S = 0.0f;
-        int IDX = 0x7fffffff;
-        __syncthreads();
-        if (n > 0) merge_records<METHOD, TB>(kp.blk_recs + ((size_t)r * kp.nblk + lo) * kp.blk_rec_stride, n, kp.blk_rec_stride, kp.P, s, M, IDX, S);
-        if (t == 0) { part[REC_M] = M; part[REC_IDX] = __int_as_float(IDX); part[REC_S] = S; part[REC_PAD] = 0.0f; }
-        if (METHOD != RANDOM_SAMPLING)
-            for (int p = t; p < kp.P; p += TB) part[REC_V + p] = n > 0 ? s.v[p] : 0.0f;
+        const int per = (kp.nblk + TAIL_NPART - 1) / TAIL_NPART;           // block records per partial record
+        for (int j = mb; j < TAIL_NPART; j += (NB < 2 ? 1 : NBM)) {
+            const int lo = j * per, n = kp.nblk - lo < per ? kp.nblk - lo : per;
+            float *part = kp.part_recs + ((size_t)r * TAIL_NPART + j) * kp.blk_rec_stride;
+            float M = CUDART_INF_F, S = 0.0f;
+            int IDX = 0x7fffffff;
+            __syncthreads();
+            if (n > 0) merge_records<METHOD, TB>(kp.blk_recs + ((size_t)r * kp.nblk + lo) * kp.blk_rec_stride, n, kp.blk_rec_stride, kp.P, s, M, IDX, S);
+            if (t == 0) { part[REC_M] = M; part[REC_IDX] = __int_as_float(IDX); part[REC_S] = S; part[REC_PAD] = 0.0f; }
+            if (METHOD != RANDOM_SAMPLING)
+                for (int p = t; p < kp.P; p += TB) part[REC_V + p] = n > 0 ? s.v[p] : 0.0f;
+        }
         if (mb == 0) phase_mark(kp, 5);
     }
     __syncthreads();
@@ -271,7 +275,7 @@ __global__ void __launch_bounds__(TAIL_TB, 1) tail_kernel(const __grid_constant_
     // ---- 3. last block: the tick's inputs, the merged record, the exact elite set, then as the fused kernel ----
     phase_mark(kp, 1);
     float M, S; int IDX;
-    merge_records<METHOD, TB>(kp.part_recs + (size_t)r * NB * kp.blk_rec_stride, NB < 2 ? 1 : NBM, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
+    merge_records<METHOD, TB>(kp.part_recs + (size_t)r * TAIL_NPART * kp.blk_rec_stride, TAIL_NPART, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
     float *rec = kp.shard_send + (size_t)r * kp.shard_rec_stride;
     if (t == 0) { rec[REC_M] = M; rec[REC_IDX] = __int_as_float(IDX); rec[REC_S] = S; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)

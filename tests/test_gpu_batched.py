@@ -50,10 +50,11 @@ def test_each_robot_of_a_batch_equals_the_oracle(built, method, adaptive):
     assert np.all(np.isfinite(out[0])) and np.all(np.isfinite(out[3]))
 
 
+@pytest.mark.parametrize('R,N', [(8, 1000), (12, 25000)])
 @pytest.mark.parametrize('method', ['mppi', 'cem_mppi'])
-def test_result_does_not_depend_on_the_partition(built, method):
-    """8 robots in one handle == the same robots split 3 + 5 (two 'ranks') == one handle per robot, bit for bit."""
-    R, N = 8, 1000
+def test_result_does_not_depend_on_the_partition(built, method, R, N):
+    """R robots in one handle == the same robots split 3 + (R - 3) (two 'ranks') == one handle per robot, bit for bit.
+    (12, 25000): two-stage launches whose tail kernel runs with a different number of blocks per robot in every grouping.)"""
     cfg = qp.SamplerConfig.for_robot('go2', sampling_method=method, control_parametrization='linear_spline',
                                      num_parallel_computations=N, lanes_per_sample=1)
     st, rf, cs, ph, _ = _scenarios('go2', R)
@@ -67,7 +68,7 @@ def test_result_does_not_depend_on_the_partition(built, method):
         return [np.concatenate([o[i] for o in outs]) for i in range(len(outs[0]))]
 
     whole = run([(0, R)])
-    for groups in ([(0, 3), (3, 8)], [(r, r + 1) for r in range(R)], [partition_robots(R, g, 4) for g in range(4)]):
+    for groups in ([(0, 3), (3, R)], [(r, r + 1) for r in range(R)], [partition_robots(R, g, 4) for g in range(4)]):
         part = run(groups)
         for a, b in zip(whole, part):
             np.testing.assert_array_equal(a, b)
