@@ -480,7 +480,16 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
         const bool x2_ok = !cfg->adaptive && smem_floats((int)x2_in_stride, h->P, XS, XTS) * sizeof(float) <= 113 * 1024;
         if (x2_ok && lps == 2) h->lanes = 2;
     }
-    plan_blocks(h->n_local, h->lanes, &kp.iters, &kp.nblk);
+    plan_blocks(h->n_local, h->lanes, &kp.iters_rec, &kp.nrec);          // record structure: a function of n_local only
+    {   // Batched launches with many waves of blocks let a block walk k record groups: the packet staging, the yaw sine
+        // and the ticket are paid once per block (3-5 % of a one-tile block's life).  The RECORDS stay those of k = 1, so
+        // results do not depend on it (tests/test_gpu_batched.py::test_result_does_not_depend_on_the_partition).
+        const long long blocks = (long long)h->R * kp.nrec;
+        const int k = h->R > 1 ? (blocks / 4 >= 2 * 592 ? 4 : (blocks / 2 >= 2 * 592 ? 2 : 1)) : 1;
+        const int tiles = (h->n_local + samples_per_tile(h->lanes) - 1) / samples_per_tile(h->lanes);
+        kp.iters = kp.iters_rec * k;
+        kp.nblk = (tiles + kp.iters - 1) / kp.iters;
+    }
     // sample per thread + noise helper threads (tick_kernel_h): one controller, one tile per block, no more blocks than SMs
     h->helpers = (h->lanes == 1 && (lps == 0 || lps == 14) && h->R == 1 && kp.iters == 1 && kp.nblk <= 148);
     kp.elite_k = elite_k;
@@ -540,7 +549,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
                                : (h->lanes == 4 ? g_quad_table : (h->helpers ? g_tick_h_table : g_tick_table))[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->finish_fn = g_finish_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
     h->tail_fn = g_tail_table[cfg->parametrization][cfg->adaptive ? 1 : 0][cfg->method];
-    if (kp.nblk >= QPMPC_TAIL_MIN_BLOCKS) h->tail_nb = std::max(1, std::min(TAIL_MAX_NB, 296 / h->R));
+    if (kp.nrec >= QPMPC_TAIL_MIN_BLOCKS) h->tail_nb = std::max(1, std::min(TAIL_MAX_NB, 296 / h->R));
 #define CKH(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { free_handle(h); return fail(QPMPC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
     CKH(cudaFuncSetAttribute((const void *)h->tick_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
     CKH(cudaFuncSetAttribute((const void *)h->finish_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->finish_smem_bytes));
@@ -560,7 +569,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     CKH(cudaMalloc((void **)&h->d_in, R * kp.in_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_out, R * kp.out_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_costs, R * (size_t)h->N * sizeof(float)));
-    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nblk, ((h->N + samples_per_tile(h->lanes) - 1) / samples_per_tile(h->lanes))) * kp.blk_rec_stride * sizeof(float)));
+    CKH(cudaMalloc((void **)&h->d_blk, R * (size_t)std::max(kp.nrec, ((h->N + samples_per_tile(h->lanes) - 1) / samples_per_tile(h->lanes))) * kp.blk_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_send, R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_recv, (size_t)W * R * kp.shard_rec_stride * sizeof(float)));
     CKH(cudaMalloc((void **)&h->d_counters, R * sizeof(unsigned int)));
@@ -957,7 +966,7 @@ static int validate_one(const qpmpc_handle *h, int r, const qpmpc_tick_in *in, u
 static void offset_robots(KParams &kp, int r0) {
     kp.in += (size_t)r0 * kp.in_stride; kp.out += (size_t)r0 * kp.out_stride;
     kp.costs += (size_t)r0 * kp.n_local;
-    kp.blk_recs += (size_t)r0 * kp.nblk * kp.blk_rec_stride;
+    kp.blk_recs += (size_t)r0 * kp.nrec * kp.blk_rec_stride;
     kp.shard_send += (size_t)r0 * kp.shard_rec_stride;
     kp.counters += r0;
     if (kp.cem_hist) kp.cem_hist += (size_t)r0 * (kp.tail_nb > 0 ? CEM_BINS_FINE : CEM_BINS);
@@ -1397,6 +1406,7 @@ extern "C" int qpmpc_rollout(qpmpc_handle *h, const float *state, const float *r
     KParams kp = h->kp;
     kp.mode = MODE_ROLLOUT; kp.n_local = h->N; kp.sample_base = 0; kp.fused_finish = 0;
     plan_blocks(h->N, h->lanes, &kp.iters, &kp.nblk);
+    kp.iters_rec = kp.iters; kp.nrec = kp.nblk;
     const size_t per = (size_t)h->N * h->P;
     rc = ensure_noise(h, per);
     if (rc) return rc;

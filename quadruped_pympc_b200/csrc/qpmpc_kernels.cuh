@@ -47,6 +47,8 @@ struct KParams {
     int H, ns, P, P_leg;
     int iters;         // tiles per block
     int nblk;          // blocks per robot
+    int nrec;          // block records per robot: one per group of `iters_rec` tiles (depends on n_local only, so that the
+    int iters_rec;     //   merge order -- and with it every result bit -- is the same however many tiles a block walks)
     int elite_k;
     int mode;          // MODE_TICK | MODE_ROLLOUT
     int noise_mode;    // NOISE_PHILOX | NOISE_INJECTED

@@ -285,14 +285,20 @@ __global__ void __launch_bounds__(QTB, 2) tick_kernel_quad(const __grid_constant
             }
         }
         if (lex_less(cmin, imin, m_run, idx_run)) { m_run = cmin; idx_run = imin; }   // running (min, argmin), S:690
+        // one record per group of kp.iters_rec tiles (or at the shard's last tile): a block that walks several groups
+        // (batched launches amortise their staging that way) leaves exactly the records one-group blocks would
+        const int T = blk * kp.iters + it;
+        if ((T + 1) % kp.iters_rec == 0 || (T + 1) * QS >= kp.n_local) {
+            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + T / kp.iters_rec) * kp.blk_rec_stride;
+            if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
+            if (METHOD != RANDOM_SAMPLING)
+                for (int p = t; p < kp.P; p += QTB) { rec[REC_V + p] = s.v[p]; s.v[p] = 0.0f; }
+            m_run = CUDART_INF_F; s_run = 0.0f; idx_run = 0x7fffffff;
+        }
         __syncthreads();
     }
     if (kp.mode == MODE_ROLLOUT) return;
     if (blk == 0) phase_mark(kp, 4);
-    float *rec = kp.blk_recs + ((size_t)r * kp.nblk + blk) * kp.blk_rec_stride;
-    if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
-    if (METHOD != RANDOM_SAMPLING)
-        for (int p = t; p < kp.P; p += QTB) rec[REC_V + p] = s.v[p];
     if (kp.defer_tail) return;                          // large launches: tail_kernel (qpmpc_tail.cuh) finishes the tick
     // release / acquire around the ticket by ONE thread between two block barriers (the shape of cooperative groups'
     // grid sync): the barrier orders the block's record stores before thread 0's fence, which is cumulative; the last

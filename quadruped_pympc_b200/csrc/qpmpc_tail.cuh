@@ -249,14 +249,14 @@ __global__ void __launch_bounds__(TAIL_TB, 1) tail_kernel(const __grid_constant_
     // ---- 2. this block's slice of the block records -> one partial record ----
     if (blk >= NBF || NB < 2) {
         const int mb = NB < 2 ? 0 : blk - NBF;
-        const int per = (kp.nblk + TAIL_NPART - 1) / TAIL_NPART;           // block records per partial record
+        const int per = (kp.nrec + TAIL_NPART - 1) / TAIL_NPART;           // block records per partial record
         for (int j = mb; j < TAIL_NPART; j += (NB < 2 ? 1 : NBM)) {
-            const int lo = j * per, n = kp.nblk - lo < per ? kp.nblk - lo : per;
+            const int lo = j * per, n = kp.nrec - lo < per ? kp.nrec - lo : per;
             float *part = kp.part_recs + ((size_t)r * TAIL_NPART + j) * kp.blk_rec_stride;
             float M = CUDART_INF_F, S = 0.0f;
             int IDX = 0x7fffffff;
             __syncthreads();
-            if (n > 0) merge_records<METHOD, TB>(kp.blk_recs + ((size_t)r * kp.nblk + lo) * kp.blk_rec_stride, n, kp.blk_rec_stride, kp.P, s, M, IDX, S);
+            if (n > 0) merge_records<METHOD, TB>(kp.blk_recs + ((size_t)r * kp.nrec + lo) * kp.blk_rec_stride, n, kp.blk_rec_stride, kp.P, s, M, IDX, S);
             if (t == 0) { part[REC_M] = M; part[REC_IDX] = __int_as_float(IDX); part[REC_S] = S; part[REC_PAD] = 0.0f; }
             if (METHOD != RANDOM_SAMPLING)
                 for (int p = t; p < kp.P; p += TB) part[REC_V + p] = n > 0 ? s.v[p] : 0.0f;

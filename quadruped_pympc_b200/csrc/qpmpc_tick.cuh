@@ -269,7 +269,7 @@ template <int METHOD, int NT>
 __device__ void shard_reduce(const KParams &kp, int r, const Smem &s, float &M, int &IDX, float &S) {
     constexpr int TB = NT;
     const int t = threadIdx.x;
-    merge_records<METHOD, NT>(kp.blk_recs + (size_t)r * kp.nblk * kp.blk_rec_stride, kp.nblk, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
+    merge_records<METHOD, NT>(kp.blk_recs + (size_t)r * kp.nrec * kp.blk_rec_stride, kp.nrec, kp.blk_rec_stride, kp.P, s, M, IDX, S, &kp);
     float *rec = kp.shard_send + (size_t)r * kp.shard_rec_stride;
     if (t == 0) { rec[REC_M] = M; rec[REC_IDX] = __int_as_float(IDX); rec[REC_S] = S; rec[REC_PAD] = 0.0f; }
     if (METHOD != RANDOM_SAMPLING)
@@ -692,14 +692,20 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
             }
         }
         if (lex_less(cmin, imin, m_run, idx_run)) { m_run = cmin; idx_run = imin; }   // running (min, argmin), S:690
+        // one record per group of kp.iters_rec tiles (or at the shard's last tile): a block that walks several groups
+        // (batched launches amortise their staging that way) leaves exactly the records one-group blocks would
+        const int T = blk * kp.iters + it;
+        if ((T + 1) % kp.iters_rec == 0 || (T + 1) * TB >= kp.n_local) {
+            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + T / kp.iters_rec) * kp.blk_rec_stride;
+            if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
+            if (METHOD != RANDOM_SAMPLING)
+                for (int p = t; p < kp.P; p += TB) { rec[REC_V + p] = s.v[p]; s.v[p] = 0.0f; }
+            m_run = CUDART_INF_F; s_run = 0.0f; idx_run = 0x7fffffff;
+        }
         __syncthreads();
     }
     if (kp.mode == MODE_ROLLOUT) return;
     if (blk == 0) phase_mark(kp, 4);
-    float *rec = kp.blk_recs + ((size_t)r * kp.nblk + blk) * kp.blk_rec_stride;
-    if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
-    if (METHOD != RANDOM_SAMPLING)
-        for (int p = t; p < kp.P; p += TB) rec[REC_V + p] = s.v[p];
     if (kp.defer_tail) return;                          // large launches: tail_kernel (qpmpc_tail.cuh) finishes the tick
     // release / acquire around the ticket by ONE thread between two block barriers (the shape of cooperative groups'
     // grid sync): the barrier orders the block's record stores before thread 0's fence, which is cumulative; the last
