@@ -118,15 +118,15 @@ def test_device_resident_sampling_iterations_equal_the_host_loop(built, method, 
     assert host.last_best_index == dev.last_best_index
 
 
-@pytest.mark.parametrize('lanes', [1, 4, 14])
+@pytest.mark.parametrize('lanes,N', [(1, 2500), (4, 2500), (14, 2500), (1, 26000)])
 @pytest.mark.parametrize('method,adaptive,iters', [('random_sampling', False, 1), ('mppi', False, 3), ('cem_mppi', False, 2),
                                                    ('mppi', True, 2), ('cem_mppi', True, 1)])
-def test_stateful_step_equals_the_interface_block(built, method, adaptive, iters, lanes):
+def test_stateful_step_equals_the_interface_block(built, method, adaptive, iters, lanes, N):
     """`step()` (device-resident best / sigma / key counter / previous contact, host prep done in the
     kernel's staging) against the block I:118-168 driven from the host with the same class, over ticks that contain
     lift-offs and touch-downs.  Must agree bit for bit, including the carried state."""
-    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=2500,
-              num_sampling_iterations=iters, optimize_step_freq=adaptive, lanes_per_sample=lanes)
+    kw = dict(sampling_method=method, control_parametrization='cubic_spline', num_parallel_computations=N,
+              num_sampling_iterations=iters, optimize_step_freq=adaptive, lanes_per_sample=lanes)   # N = 26 000: two-stage launches
     cem = method == 'cem_mppi'
     host = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
     dev = qp.Sampling_MPC(qp.SamplerConfig.for_robot('go2', **kw))
