@@ -331,7 +331,10 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         out[OUT_BEST + p] = s.v[p];
         if (carry) carry[p] = s.v[p];
     }
-    if (t == 0) {
+    // The serial read-out (GRFs at step 0, predicted state, scalars, carried key / contact) is ~300 dependent instructions of
+    // ONE thread.  For CEM it runs on the LAST thread while the low threads regenerate the elite noise rows of the first
+    // refit chunk (k = 10, or 200 rows on the 256-thread tail kernel: that thread has no row), otherwise right here.
+    auto readout = [&]() {
         tail_grf_pred<PARAM>(kp, s.in, s.yaw, s.v, out);
         out[OUT_BESTCOST] = M;
         out[OUT_BESTIDX] = __int_as_float(IDX);
@@ -349,8 +352,10 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
         } else if (kp.carry_best) {
             const_cast<float *>(kp.in)[(size_t)r * kp.in_stride + IN_TICK] = __uint_as_float(tick + 1u);
         }
-        phase_mark(kp, 6);
-    }
+        if (kp.phase_ns != nullptr && blockIdx.y == 0) { unsigned long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns)); kp.phase_ns[6] = ns; }
+    };
+    const bool late_readout = (METHOD == CEM_MPPI) && ((kp.elite_k < kp.N ? kp.elite_k : kp.N) < NT);
+    if (t == NT - 1 && !late_readout) readout();
     if (METHOD != CEM_MPPI) return;
     // ---- CEM elite refit ----
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(s.tile);
@@ -390,7 +395,8 @@ __device__ void finish(const KParams &kp, int r, const Smem &s, const float *rec
     for (int j = 0; j < MAXV; ++j) { mean_acc[j] = 0.0f; m2_acc[j] = 0.0f; }
     for (int base = 0; base < k; base += TB) {
         const int cnt = (k - base) < TB ? (k - base) : TB;
-        __syncthreads();
+        if (base > 0) __syncthreads();                         // (the first chunk follows the barrier above)
+        if (base == 0 && late_readout && t == NT - 1) readout();
         const int my_idx = (t < cnt) ? s.idx[base + t] : -1;
         if (t < cnt) {
             float *tcol = s.tile + t;
