@@ -293,13 +293,19 @@ __global__ void __launch_bounds__(TAIL_TB, 1) tail_kernel(const __grid_constant_
         __syncthreads();
         for (unsigned int i = t; i < nsel; i += TB) { const unsigned int slot = atomicAdd(&misc[3], 1u); if (slot < MAX_ELITE) keys[slot] = __ldcg(sel + i); }
         __syncthreads();
-        const unsigned int got = misc[3];                 // == k
+        const unsigned int got = misc[3] < (unsigned int)MAX_ELITE ? misc[3] : (unsigned int)MAX_ELITE;   // == k
+        // rank sort (keys are unique: the index is part of the key): thread t places keys[t] at the number of smaller keys.
+        // 2 barriers instead of the 36 barrier-separated stages of a 256-key bitonic network.
+        static_assert(TAIL_TB >= MAX_ELITE, "one thread per elite key");
+        unsigned long long *sorted = keys + MAX_ELITE;    // (the candidate list is dead by now)
+        const unsigned long long mine = t < (int)got ? keys[t] : ~0ull;
+        int rank = 0;
+        for (unsigned int j = 0; j < got; ++j) rank += (keys[j] < mine) ? 1 : 0;
         __syncthreads();
-        for (int i = (int)got + t; i < MAX_ELITE; i += TB) keys[i] = ~0ull;
+        if (t < (int)got) sorted[rank] = mine;
         __syncthreads();
-        bitonic_sort_u64<TB>(keys, MAX_ELITE);
         for (int j = t; j < kp.elite_k; j += TB) {
-            const unsigned long long key = j < k ? keys[j] : ~0ull;
+            const unsigned long long key = j < k && j < (int)got ? sorted[j] : ~0ull;
             rec[REC_V + kp.P + 2 * j] = __uint_as_float((unsigned int)(key >> 32));
             rec[REC_V + kp.P + 2 * j + 1] = __uint_as_float((unsigned int)(key & 0xffffffffu));
         }
