@@ -379,6 +379,10 @@ __device__ __forceinline__ Body load_body(const float *s) { return load_body_t<f
 struct Knots1 {                       // one sample per thread: tile column `tcol`, row stride TS
     const float *s_best, *tcol;
     __device__ __forceinline__ float operator()(int p) const { return qadd(tcol[p * TS], s_best[p]); }
+    // knots px (of the x axis) and py (of the y axis) as one packed add
+    __device__ __forceinline__ XY<float> pair(int px, int py) const {
+        return xy_add(xy_make(tcol[px * TS], tcol[py * TS]), xy_make(s_best[px], s_best[py]));
+    }
 };
 
 // Fixed-gait rollout (S:316-496): every leg's spline clock is the step n, contact table shared by all samples,
@@ -395,7 +399,9 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
     const int H = kp.H, PL = kp.P_leg;
     constexpr float third = 1.0f / 3.0f;   // forces_z / forces_x = 30/10, S:388
     // hoisted knots of the current spline chunk (cubic: k1, phi, k2, phi_next ; linear: k0, k1)
-    T ka[4][3], kb[4][3], kc[4][3], kd[4][3];
+    // (x and y axes as XY units: one packed operation for both when T = float, see qpmpc_math.cuh; z on its own)
+    XY<T> kaxy[4], kbxy[4], kcxy[4], kdxy[4];
+    T kaz[4], kbz[4], kcz[4], kdz[4];
     int cur = -1;
 #pragma unroll 1
     for (int n = 0; n < H; ++n) {
@@ -405,21 +411,27 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
                 cur = idx;
 #pragma unroll
                 for (int l = 0; l < 4; ++l) {
-#pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        if (PARAM == CUBIC) {                 // S:219-255
-                            const int s0 = l * PL + 10 * idx + 4 * a;
-                            const T p0 = knot(s0), p1 = knot(s0 + 1), p2 = knot(s0 + 2), p3 = knot(s0 + 3);
-                            const T d10 = qsub(p1, p0), d21 = qsub(p2, p1), d32 = qsub(p3, p2);
-                            ka[l][a] = p1;
-                            kb[l][a] = qmul(qadd(d21, d10), 0.5f);
-                            kc[l][a] = p2;
-                            kd[l][a] = qmul(qadd(d32, d21), 0.5f);
-                        } else {                              // S:196-199
-                            const int s0 = l * PL + idx + (kp.ns + 1) * a;
-                            ka[l][a] = knot(s0);
-                            kb[l][a] = knot(s0 + 1);
-                        }
+                    if (PARAM == CUBIC) {                     // S:219-255
+                        const int sx = l * PL + 10 * idx, sy = sx + 4, sz = sx + 8;
+                        const XY<T> p0 = knot.pair(sx, sy), p1 = knot.pair(sx + 1, sy + 1), p2 = knot.pair(sx + 2, sy + 2),
+                                    p3 = knot.pair(sx + 3, sy + 3);
+                        const XY<T> d10 = xy_sub(p1, p0), d21 = xy_sub(p2, p1), d32 = xy_sub(p3, p2);
+                        kaxy[l] = p1;
+                        kbxy[l] = xy_mul(xy_add(d21, d10), 0.5f);
+                        kcxy[l] = p2;
+                        kdxy[l] = xy_mul(xy_add(d32, d21), 0.5f);
+                        const T z0 = knot(sz), z1 = knot(sz + 1), z2 = knot(sz + 2), z3 = knot(sz + 3);
+                        const T e10 = qsub(z1, z0), e21 = qsub(z2, z1), e32 = qsub(z3, z2);
+                        kaz[l] = z1;
+                        kbz[l] = qmul(qadd(e21, e10), 0.5f);
+                        kcz[l] = z2;
+                        kdz[l] = qmul(qadd(e32, e21), 0.5f);
+                    } else {                                  // S:196-199
+                        const int sx = l * PL + idx, sy = sx + (kp.ns + 1), sz = sy + (kp.ns + 1);
+                        kaxy[l] = knot.pair(sx, sy);
+                        kbxy[l] = knot.pair(sx + 1, sy + 1);
+                        kaz[l] = knot(sz);
+                        kbz[l] = knot(sz + 1);
                     }
                 }
             }
@@ -431,20 +443,20 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
 #pragma unroll
         for (int l = 0; l < 4; ++l) {
             if (cm & (1 << l)) {
-                T fx, fy, fz;
+                XY<T> fxy;
+                T fz;
                 if (PARAM == CUBIC) {
-                    fx = qfma(kd[l][0], w3, qfma(kc[l][0], w2, qfma(kb[l][0], w1, qmul(ka[l][0], w0))));
-                    fy = qfma(kd[l][1], w3, qfma(kc[l][1], w2, qfma(kb[l][1], w1, qmul(ka[l][1], w0))));
-                    fz = qfma(kd[l][2], w3, qfma(kc[l][2], w2, qfma(kb[l][2], w1, qmul(ka[l][2], w0))));
+                    fxy = xy_fma(kdxy[l], w3, xy_fma(kcxy[l], w2, xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0))));
+                    fz = qfma(kdz[l], w3, qfma(kcz[l], w2, qfma(kbz[l], w1, qmul(kaz[l], w0))));
                 } else if (PARAM == LINEAR) {
-                    fx = qfma(kb[l][0], w1, qmul(ka[l][0], w0));
-                    fy = qfma(kb[l][1], w1, qmul(ka[l][1], w0));
-                    fz = qfma(kb[l][2], w1, qmul(ka[l][2], w0));
+                    fxy = xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0));
+                    fz = qfma(kbz[l], w1, qmul(kaz[l], w0));
                 } else {                                      // S:259-268
-                    fx = knot(l * PL + n); fy = knot(l * PL + n + H); fz = knot(l * PL + n + 2 * H);
+                    fxy = knot.pair(l * PL + n, l * PL + n + H); fz = knot(l * PL + n + 2 * H);
                 }
                 fz = qadd(fz, fref);                          // S:382-385
-                fx = qmul(fx, third); fy = qmul(fy, third);   // S:388-402 with contact == 1
+                fxy = xy_mul(fxy, third);                     // S:388-402 with contact == 1
+                T fx = fxy.x(), fy = fxy.y();
                 clamp_leg(kp, fx, fy, fz);                    // S:405-409
                 add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }

@@ -57,6 +57,33 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 __device__ __forceinline__ float2 rcp_approx(float2 x) { return make_float2(rcp_approx(x.x), rcp_approx(x.y)); }
 
+// ---- the (x, y) components of one quantity as a unit --------------------------------------------------------------
+// For T = float the x and y components of a leg's spline coefficients / force travel in ONE 64-bit register pair, so
+// that the spline evaluation of the sample-per-thread kernels issues FFMA2 / FMUL2 / FADD2 too (the same IEEE operation
+// per component: results are bit-identical to evaluating x and y separately).  For T = float2 (two samples per thread)
+// the components stay two packed values.
+template <class T> struct XY;
+template <> struct XY<float> {
+    float2 v;
+    __device__ __forceinline__ float x() const { return v.x; }
+    __device__ __forceinline__ float y() const { return v.y; }
+};
+template <> struct XY<float2> {
+    float2 a, b;
+    __device__ __forceinline__ float2 x() const { return a; }
+    __device__ __forceinline__ float2 y() const { return b; }
+};
+__device__ __forceinline__ XY<float> xy_make(float x, float y) { XY<float> r; r.v = make_float2(x, y); return r; }
+__device__ __forceinline__ XY<float2> xy_make(float2 x, float2 y) { XY<float2> r; r.a = x; r.b = y; return r; }
+__device__ __forceinline__ XY<float> xy_add(XY<float> p, XY<float> q) { XY<float> r; r.v = __fadd2_rn(p.v, q.v); return r; }
+__device__ __forceinline__ XY<float2> xy_add(XY<float2> p, XY<float2> q) { return xy_make(qadd(p.a, q.a), qadd(p.b, q.b)); }
+__device__ __forceinline__ XY<float> xy_sub(XY<float> p, XY<float> q) { XY<float> r; r.v = __fadd2_rn(p.v, qneg(q.v)); return r; }
+__device__ __forceinline__ XY<float2> xy_sub(XY<float2> p, XY<float2> q) { return xy_make(qsub(p.a, q.a), qsub(p.b, q.b)); }
+__device__ __forceinline__ XY<float> xy_mul(XY<float> p, float s) { XY<float> r; r.v = __fmul2_rn(p.v, bc2(s)); return r; }
+__device__ __forceinline__ XY<float2> xy_mul(XY<float2> p, float s) { return xy_make(qmul(p.a, s), qmul(p.b, s)); }
+__device__ __forceinline__ XY<float> xy_fma(XY<float> p, float s, XY<float> c) { XY<float> r; r.v = __ffma2_rn(p.v, bc2(s), c.v); return r; }
+__device__ __forceinline__ XY<float2> xy_fma(XY<float2> p, float s, XY<float2> c) { return xy_make(qfma(p.a, s, c.a), qfma(p.b, s, c.b)); }
+
 // ---- sine / cosine -------------------------------------------------------------------------------------------
 // |x| <= pi/4 (every sane rollout): the same minimax polynomials sincosf evaluates after its range reduction, without the
 // reduction and quadrant logic (~11 instructions instead of ~35, same <= 1 ulp accuracy); larger angles (diverged

@@ -26,6 +26,7 @@ struct Knots2 {
     __device__ __forceinline__ float2 operator()(int p) const {
         return qadd(*reinterpret_cast<const float2 *>(tpair + p * XTS), s_best[p]);
     }
+    __device__ __forceinline__ XY<float2> pair(int px, int py) const { return xy_make((*this)(px), (*this)(py)); }
 };
 
 // compact_weights for two samples per thread: (weight, slot) pairs of the non-zero weights in ascending slot order
