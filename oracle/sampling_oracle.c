@@ -378,12 +378,12 @@ static inline float u01_from_bits(uint32_t b) {       /* mantissa trick of jax.r
 }
 
 /* Box-Muller exactly as the device does it (csrc/qpmpc_kernels.cuh box_muller16), with libm in place of the SFU
- * approximations: ONE word -> two normals (radius from the low 16 bits, angle from the high 16 bits), the row's scale
- * folded into the radius constant c = -2 ln2 * s^2. */
+ * approximations: ONE word -> two normals (radius from bits 7..22, angle from the other 16 bits = bits 7..22 of the word
+ * rotated by 16), the row's scale folded into the radius constant c = -2 ln2 * s^2. */
 static inline void box_muller16(uint32_t w, float c, float *z0, float *z1) {
     union { uint32_t u; float f; } ua, ub;
-    ua.u = ((w << 7) & 0x007fff80u) | 0x3F800000u;
-    ub.u = ((w >> 9) & 0x007fff80u) | 0x40000000u;
+    ua.u = (w & 0x007fff80u) | 0x3F800000u;
+    ub.u = (((w << 16) | (w >> 16)) & 0x007fff80u) | 0x40000000u;
     float u = 2.0f - ua.f;
     float th = ub.f * 3.14159265f + -9.42477796f;
     float r = sqrtf(c * log2f(u));

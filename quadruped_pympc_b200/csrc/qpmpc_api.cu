@@ -510,6 +510,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     inv3f(cfg->inertia, kp.Iinv);                                                   // M:56
     memcpy(kp.qd, cfg->q_diag, sizeof(kp.qd));
     kp.q_xyyaw = (cfg->q_diag[0] != 0.f || cfg->q_diag[1] != 0.f || cfg->q_diag[8] != 0.f) ? 1 : 0;
+    kp.bm_bits[0] = 0x3F800000u; kp.bm_bits[1] = 0x40000000u;
     kp.mpc_dt = cfg->dts[H - 1];                                                    // A:179: pgg mpc_dt = self.dt
     kp.duty = cfg->pgg_duty_factor;
     memcpy(kp.sigma_rs, cfg->sigma_random_sampling, sizeof(kp.sigma_rs));
@@ -526,10 +527,14 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
         kp.sp_index[n] = (unsigned char)idx;
         const float q = stepf / denom_fixed - (float)idx;                           // S:191-194
         if (cfg->parametrization == QPMPC_CUBIC_SPLINE) {                           // S:222-225
-            kp.basis[n][0] = 2.0f * q * q * q - 3.0f * q * q + 1.0f;
-            kp.basis[n][1] = (q * q * q - 2.0f * q * q + q) * 1.0f;
-            kp.basis[n][2] = -2.0f * q * q * q + 3.0f * q * q;
-            kp.basis[n][3] = (q * q * q - q * q) * 1.0f;
+            const double a = 2.0f * q * q * q - 3.0f * q * q + 1.0f, b = (q * q * q - 2.0f * q * q + q) * 1.0f;
+            const double c = -2.0f * q * q * q + 3.0f * q * q, d = (q * q * q - q * q) * 1.0f;
+            // f = a p1 + b phi + c p2 + d phi_next with phi = (p2 - p0) / 2, phi_next = (p3 - p1) / 2 (S:227-255),
+            // collected per knot: the kernels evaluate f = sum_i w_i p_i on the four knots of the chunk directly
+            kp.basis[n][0] = (float)(-0.5 * b);
+            kp.basis[n][1] = (float)(a - 0.5 * d);
+            kp.basis[n][2] = (float)(c + 0.5 * b);
+            kp.basis[n][3] = (float)(0.5 * d);
         } else if (cfg->parametrization == QPMPC_LINEAR_SPLINE) {                   // S:197
             kp.basis[n][0] = 1.0f - q; kp.basis[n][1] = q;
         }

@@ -63,12 +63,13 @@ struct KParams {
     float I[9], Iinv[9];
     float qd[12];
     int q_xyyaw;                            // 1: q_diag weights x, y or yaw (the reference's Q does not)
+    uint32_t bm_bits[2];                    // 0x3F800000, 0x40000000: exponent patterns of box_muller16 (see there)
     float mpc_dt, duty;
     float sigma_rs[3], sigma_mppi;
     float freq_avail[3];
     float inv_ns, denom_fixed_inv;          // 1/ns ; 1/(H/ns)
     float dt[MAX_H];
-    float basis[MAX_H][4];                  // fixed gait: cubic (a,b,c,d) | linear (1-q, q, -, -) per step
+    float basis[MAX_H][4];                  // fixed gait, per step: cubic Hermite weights of the chunk's knots p0..p3 | linear (1-q, q, -, -)
     float bounds[MAX_NS + 1];               // linspace(0,H,ns+1), S:187
     unsigned char sp_index[MAX_H];          // fixed gait: spline chunk index per step, S:189
     const float *in;                        // [R][in_stride]
@@ -149,15 +150,25 @@ __device__ __forceinline__ float u01_from_bits(uint32_t b) { return __uint_as_fl
 
 // Two normals from ONE 32-bit word (Box-Muller on the SFU: lg2 / sqrt / sin / cos approximations): a Philox block of
 // four words yields EIGHT normals (r2: it yielded four; the generator was 22 % of the executed instructions).
-//   radius from the low 16 bits:  u = 2 - [1,2) (step 2^-16) in [2^-16, 1]  ->  r = sqrt(c * log2 u),  c = -2 ln2 * s^2
-//                                 (the row's scale s folded into the constant);  |z| <= 4.71 s
-//   angle  from the high 16 bits: th = pi * ([2,4) - 3)  in [-pi, pi), 65 536 directions
+//   radius from bits 7..22 (in place: they ARE the 16 leading mantissa bits):  u = 2 - [1,2) (step 2^-16) in [2^-16, 1]
+//                                 ->  r = sqrt(c * log2 u),  c = -2 ln2 * s^2 (the row's scale s folded into the
+//                                 constant);  |z| <= 4.71 s
+//   angle  from the other 16 bits (0..6 and 23..31: the word rotated by 16 puts them on the mantissa):
+//                                 th = pi * ([2,4) - 3)  in [-pi, pi), 65 536 directions
+// Per word: one LOP3 (mask | exponent) for the radius, one rotate + one LOP3 for the angle.  `one` / `two` are the
+// exponent patterns 0x3F800000 / 0x40000000 handed in as kernel parameters (KParams::bm_bits): LOP3 encodes a single
+// immediate, so as literals the compiler splits each (w & mask) | exponent into two instructions.
 // (The reference draws with jax.random.normal = sqrt(2) * erfinv(uniform), resolution 2^-23, |z| <= 5.4; only the
 //  distribution is part of the contract -- parity tests inject or export the tensor; tests/test_gpu_parity.py checks
 //  moments, tail mass and a Kolmogorov-Smirnov distance of the device's own draw.)
-__device__ __forceinline__ void box_muller16(uint32_t w, float c, float &z0, float &z1) {
-    const float u = 2.0f - __uint_as_float(((w << 7) & 0x007fff80u) | 0x3F800000u);
-    const float th = fmaf(__uint_as_float(((w >> 9) & 0x007fff80u) | 0x40000000u), 3.14159265f, -9.42477796f);
+__device__ __forceinline__ uint32_t mask_or(uint32_t a, uint32_t mask, uint32_t bits) {      // (a & mask) | bits
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(mask), "r"(bits));
+    return d;
+}
+__device__ __forceinline__ void box_muller16(uint32_t w, float c, uint32_t one, uint32_t two, float &z0, float &z1) {
+    const float u = 2.0f - __uint_as_float(mask_or(w, 0x007fff80u, one));
+    const float th = fmaf(__uint_as_float(mask_or(__funnelshift_l(w, w, 16), 0x007fff80u, two)), 3.14159265f, -9.42477796f);
     float l2, r, sn, cs;
     asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(u));
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(c * l2));
@@ -174,7 +185,7 @@ constexpr float BM_C1 = -1.38629436f;         // -2 ln 2: unit-variance normals
 //  random_sampling S:647-677: rows [1,1+k) s0*N, [1+k,1+2k) s1*N (same key => same normals), [1+2k,N) U(-s2,s2)
 //  mppi S:806-812: s*N on rows 1..N-1 ; cem_mppi S:951-958: N*sigma[p] ; row 0 is always zero.
 // NoiseRow: what depends on the row only (computed once per sample, outside the loop over quads).
-struct NoiseRow { uint32_t j; int seg; float scale, c; bool zero; };   // c = -2 ln2 * scale^2 (cem_mppi: -2 ln2)
+struct NoiseRow { uint32_t j; int seg; float scale, c; bool zero; uint32_t one, two; };   // c = -2 ln2 * scale^2 (cem_mppi: -2 ln2); one/two: box_muller16
 
 template <int METHOD>
 __device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
@@ -187,6 +198,7 @@ __device__ __forceinline__ NoiseRow noise_row(const KParams &kp, int i) {
         nr.scale = kp.sigma_rs[nr.seg];
     }
     nr.c = (METHOD == CEM_MPPI) ? BM_C1 : (BM_C1 * nr.scale) * nr.scale;
+    nr.one = kp.bm_bits[0]; nr.two = kp.bm_bits[1];
     return nr;
 }
 
@@ -205,8 +217,8 @@ __device__ __forceinline__ float4 uniform_quad(const NoiseRow &nr, uint32_t seed
 template <int METHOD>
 __device__ __forceinline__ float4 normal_quad(const NoiseRow &nr, uint32_t w0, uint32_t w1, int q, const float *s_sigma) {
     float4 v;
-    box_muller16(w0, nr.c, v.x, v.y);
-    box_muller16(w1, nr.c, v.z, v.w);
+    box_muller16(w0, nr.c, nr.one, nr.two, v.x, v.y);
+    box_muller16(w1, nr.c, nr.one, nr.two, v.z, v.w);
     if (METHOD == CEM_MPPI) {
         v.x *= s_sigma[4 * q + 0]; v.y *= s_sigma[4 * q + 1]; v.z *= s_sigma[4 * q + 2]; v.w *= s_sigma[4 * q + 3];
     }
@@ -291,9 +303,9 @@ __device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, co
                                         T &Fx, T &Fy, T &Fz, T &tx, T &ty, T &tz) {
     const T rx = qsub(foot[0], b.px), ry = qsub(foot[1], b.py), rz = qsub(foot[2], b.pz);
     Fx = qadd(Fx, fx); Fy = qadd(Fy, fy); Fz = qadd(Fz, fz);
-    tx = qadd(tx, qfms(ry, fz, qmul(rz, fy)));
-    ty = qadd(ty, qfms(rz, fx, qmul(rx, fz)));
-    tz = qadd(tz, qfms(rx, fy, qmul(ry, fx)));
+    tx = qfnma(rz, fy, qfma(ry, fz, tx));               // the moment accumulates term by term: two FMAs per component
+    ty = qfnma(rx, fz, qfma(rz, fx, ty));
+    tz = qfnma(ry, fx, qfma(rx, fy, tz));
 }
 
 // one term of e^T Q e on the state after the step, S:450-451 (the reference's Q also weights x, y, yaw with 0: kept, so
@@ -307,38 +319,35 @@ __device__ __forceinline__ void cost_term(T &c, T x, float ref, float q) {
 template <class T>
 __device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T Fy, T Fz, T tx, T ty, T tz, float dt,
                                        const float *ref, const float *s_yaw) {
-    const T ax = qmul(Fx, kp.inv_m), ay = qmul(Fy, kp.inv_m), az = qfma(Fz, kp.inv_m, -9.81f);       // M:118
     T sr, cr, sp, cp, sy, cy;
     sincos_rpy(b.roll, b.pitch, b.yaw, s_yaw, sr, cr, sp, cp, sy, cy);
-    // inverse of the conjugate Euler-rate matrix by cofactors with its structural zeros dropped, M:124-130,137
-    const T cpcr = qmul(cp, cr), cpsr = qmul(cp, sr), srsp = qmul(sr, sp), crsp = qmul(cr, sp);
-    const T det = qfma(sr, cpsr, qmul(cpcr, cr));
-    const T rd = rcp_approx(det);                        // 1 / det on the SFU (<= 1 ulp; det = cos(pitch) is O(1))
-    const T e01 = qmul(srsp, rd), e02 = qmul(crsp, rd), e11 = qmul(cpcr, rd), e12 = qmul(qneg(cpsr), rd);
-    const T e21 = qmul(sr, rd), e22 = qmul(cr, rd);
-    const T droll = qfma(e02, b.wz, qfma(e01, b.wy, b.wx));
-    const T dpitch = qfma(e12, b.wz, qmul(e11, b.wy));
-    const T dyaw = qfma(e22, b.wz, qmul(e21, b.wy));
-    // b_R_w (ZYX), M:141-155, applied to the world torque
-    const T r00 = qmul(cp, cy), r01 = qmul(cp, sy);                                   // r02 = -sp
-    const T r10 = qfms(srsp, cy, qmul(cr, sy)), r11 = qfma(srsp, sy, qmul(cr, cy));   // r12 = sr cp
-    const T r20 = qfma(crsp, cy, qmul(sr, sy)), r21 = qfms(crsp, sy, qmul(sr, cy));   // r22 = cr cp
-    const T bx = qfnma(sp, tz, qfma(r01, ty, qmul(r00, tx)));
-    const T by = qfma(cpsr, tz, qfma(r11, ty, qmul(r10, tx)));
-    const T bz = qfma(cpcr, tz, qfma(r21, ty, qmul(r20, tx)));
+    // Euler rates = inverse of the conjugate Euler-rate matrix times w, M:124-130,137.  The matrix is
+    // [[1, 0, -sp], [0, cr, cp sr], [0, -sr, cp cr]]; its inverse in closed form is [[1, sr tp, cr tp], [0, cr, -sr],
+    // [0, sr / cp, cr / cp]] (determinant cp), so the rates need one reciprocal on the SFU (<= 1 ulp) and six FMAs
+    const T swcw = qfma(cr, b.wz, qmul(sr, b.wy));
+    const T dpitch = qfnma(sr, b.wz, qmul(cr, b.wy));
+    const T dyaw = qmul(swcw, rcp_approx(cp));
+    const T droll = qfma(sp, dyaw, b.wx);
+    // b_R_w tau, M:141-155: b_R_w = Rx(roll)^T Ry(pitch)^T Rz(yaw)^T applied as three plane rotations (12 operations;
+    // forming the nine matrix entries first takes 19)
+    const T ux = qfma(sy, ty, qmul(cy, tx)), uy = qfnma(sy, tx, qmul(cy, ty));
+    const T bx = qfnma(sp, tz, qmul(cp, ux)), uz = qfma(cp, tz, qmul(sp, ux));
+    const T by = qfma(sr, uz, qmul(cr, uy)), bz = qfnma(sr, uy, qmul(cr, uz));
     // angular acceleration Iinv * (b_R_w tau - w x (I w)), M:157-159
     const T Iwx = qfma(b.wz, kp.I[2], qfma(b.wy, kp.I[1], qmul(b.wx, kp.I[0])));
     const T Iwy = qfma(b.wz, kp.I[5], qfma(b.wy, kp.I[4], qmul(b.wx, kp.I[3])));
     const T Iwz = qfma(b.wz, kp.I[8], qfma(b.wy, kp.I[7], qmul(b.wx, kp.I[6])));
-    const T hx = qsub(bx, qfms(b.wy, Iwz, qmul(b.wz, Iwy)));
-    const T hy = qsub(by, qfms(b.wz, Iwx, qmul(b.wx, Iwz)));
-    const T hz = qsub(bz, qfms(b.wx, Iwy, qmul(b.wy, Iwx)));
+    const T hx = qfma(b.wz, Iwy, qfnma(b.wy, Iwz, bx));
+    const T hy = qfma(b.wx, Iwz, qfnma(b.wz, Iwx, by));
+    const T hz = qfma(b.wy, Iwx, qfnma(b.wx, Iwy, bz));
     const T dwx = qfma(hz, kp.Iinv[2], qfma(hy, kp.Iinv[1], qmul(hx, kp.Iinv[0])));
     const T dwy = qfma(hz, kp.Iinv[5], qfma(hy, kp.Iinv[4], qmul(hx, kp.Iinv[3])));
     const T dwz = qfma(hz, kp.Iinv[8], qfma(hy, kp.Iinv[7], qmul(hx, kp.Iinv[6])));
-    // explicit Euler, M:171-172 (all derivatives from the old state)
+    // explicit Euler, M:171-172 (all derivatives from the old state); linear acceleration F / m + g (M:118) with
+    // dt / m and g dt as per-step uniforms
+    const float dtm = dt * kp.inv_m, gdt = -9.81f * dt;
     b.px = qfma(b.vx, dt, b.px); b.py = qfma(b.vy, dt, b.py); b.pz = qfma(b.vz, dt, b.pz);
-    b.vx = qfma(ax, dt, b.vx); b.vy = qfma(ay, dt, b.vy); b.vz = qfma(az, dt, b.vz);
+    b.vx = qfma(Fx, dtm, b.vx); b.vy = qfma(Fy, dtm, b.vy); b.vz = qfma(Fz, dtm, qadd(b.vz, gdt));
     b.roll = qfma(droll, dt, b.roll); b.pitch = qfma(dpitch, dt, b.pitch); b.yaw = qfma(dyaw, dt, b.yaw);
     b.wx = qfma(dwx, dt, b.wx); b.wy = qfma(dwy, dt, b.wy); b.wz = qfma(dwz, dt, b.wz);
     // e^T Q e on the state after the step, S:450-451 (diagonal Q; fixed term order)
@@ -413,19 +422,10 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
                 for (int l = 0; l < 4; ++l) {
                     if (PARAM == CUBIC) {                     // S:219-255
                         const int sx = l * PL + 10 * idx, sy = sx + 4, sz = sx + 8;
-                        const XY<T> p0 = knot.pair(sx, sy), p1 = knot.pair(sx + 1, sy + 1), p2 = knot.pair(sx + 2, sy + 2),
-                                    p3 = knot.pair(sx + 3, sy + 3);
-                        const XY<T> d10 = xy_sub(p1, p0), d21 = xy_sub(p2, p1), d32 = xy_sub(p3, p2);
-                        kaxy[l] = p1;
-                        kbxy[l] = xy_mul(xy_add(d21, d10), 0.5f);
-                        kcxy[l] = p2;
-                        kdxy[l] = xy_mul(xy_add(d32, d21), 0.5f);
-                        const T z0 = knot(sz), z1 = knot(sz + 1), z2 = knot(sz + 2), z3 = knot(sz + 3);
-                        const T e10 = qsub(z1, z0), e21 = qsub(z2, z1), e32 = qsub(z3, z2);
-                        kaz[l] = z1;
-                        kbz[l] = qmul(qadd(e21, e10), 0.5f);
-                        kcz[l] = z2;
-                        kdz[l] = qmul(qadd(e32, e21), 0.5f);
+                        // the knots of the chunk as they are: kp.basis holds the Hermite weights per KNOT (host)
+                        kaxy[l] = knot.pair(sx, sy); kbxy[l] = knot.pair(sx + 1, sy + 1);
+                        kcxy[l] = knot.pair(sx + 2, sy + 2); kdxy[l] = knot.pair(sx + 3, sy + 3);
+                        kaz[l] = knot(sz); kbz[l] = knot(sz + 1); kcz[l] = knot(sz + 2); kdz[l] = knot(sz + 3);
                     } else {                                  // S:196-199
                         const int sx = l * PL + idx, sy = sx + (kp.ns + 1), sz = sy + (kp.ns + 1);
                         kaxy[l] = knot.pair(sx, sy);

@@ -146,13 +146,23 @@ __device__ __forceinline__ bool angles_small(float a, float b, float c) {
 __device__ __forceinline__ bool angles_small(float2 a, float2 b, float2 c) {
     return fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(b.x), fabsf(b.y))), fmaxf(fabsf(c.x), fabsf(c.y))) <= 0.78539816f;
 }
+// the polynomials of two angles: for one sample per thread as ONE packed evaluation (FFMA2 / FMUL2: the same IEEE
+// operation per component, so the results are those of two scalar evaluations)
+__device__ __forceinline__ void sincos_poly_pair(float a, float b, float &sa, float &ca, float &sb, float &cb) {
+    float2 sn, cs;
+    sincos_poly<float2>(make_float2(a, b), sn, cs);
+    sa = sn.x; sb = sn.y; ca = cs.x; cb = cs.y;
+}
+__device__ __forceinline__ void sincos_poly_pair(float2 a, float2 b, float2 &sa, float2 &ca, float2 &sb, float2 &cb) {
+    sincos_poly<float2>(a, sa, ca);
+    sincos_poly<float2>(b, sb, cb);
+}
 template <class T>
 __device__ __forceinline__ void sincos_rpy(T roll, T pitch, T yaw, const float *s_yaw, T &sr, T &cr, T &sp, T &cp, T &sy, T &cy) {
     const T d = qsub(yaw, s_yaw[0]);
     if (angles_small(roll, pitch, d)) {
         T sd, cd;
-        sincos_poly<T>(roll, sr, cr);
-        sincos_poly<T>(pitch, sp, cp);
+        sincos_poly_pair(roll, pitch, sr, cr, sp, cp);
         sincos_poly<T>(d, sd, cd);
         const float s0 = s_yaw[1], c0 = s_yaw[2];
         sy = qfma(s0, cd, qmul(c0, sd));

@@ -66,11 +66,7 @@ __device__ __forceinline__ float rollout_fixed_quad(const KParams &kp, const flo
                 for (int a = 0; a < 3; ++a) {
                     if (PARAM == CUBIC) {                     // S:219-255
                         const int s0 = 10 * idx + 4 * a;
-                        const float p0 = QP_QKNOT(s0), p1 = QP_QKNOT(s0 + 1), p2 = QP_QKNOT(s0 + 2), p3 = QP_QKNOT(s0 + 3);
-                        ka[a] = p1;
-                        kb[a] = 0.5f * ((p2 - p1) + (p1 - p0));
-                        kc[a] = p2;
-                        kd[a] = 0.5f * ((p3 - p2) + (p2 - p1));
+                        ka[a] = QP_QKNOT(s0); kb[a] = QP_QKNOT(s0 + 1); kc[a] = QP_QKNOT(s0 + 2); kd[a] = QP_QKNOT(s0 + 3);
                     } else {                                  // S:196-199
                         const int s0 = idx + (kp.ns + 1) * a;
                         ka[a] = QP_QKNOT(s0);
