@@ -511,6 +511,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     memcpy(kp.qd, cfg->q_diag, sizeof(kp.qd));
     kp.q_xyyaw = (cfg->q_diag[0] != 0.f || cfg->q_diag[1] != 0.f || cfg->q_diag[8] != 0.f) ? 1 : 0;
     kp.bm_bits[0] = 0x3F800000u; kp.bm_bits[1] = 0x40000000u;
+    { const int qi[8] = {3, 4, 2, 5, 6, 7, 9, 10}; for (int k = 0; k < 8; ++k) kp.qpair[k] = cfg->q_diag[qi[k]]; }
     kp.mpc_dt = cfg->dts[H - 1];                                                    // A:179: pgg mpc_dt = self.dt
     kp.duty = cfg->pgg_duty_factor;
     memcpy(kp.sigma_rs, cfg->sigma_random_sampling, sizeof(kp.sigma_rs));

@@ -84,6 +84,16 @@ __device__ __forceinline__ XY<float2> xy_mul(XY<float2> p, float s) { return xy_
 __device__ __forceinline__ XY<float> xy_fma(XY<float> p, float s, XY<float> c) { XY<float> r; r.v = __ffma2_rn(p.v, bc2(s), c.v); return r; }
 __device__ __forceinline__ XY<float2> xy_fma(XY<float2> p, float s, XY<float2> c) { return xy_make(qfma(p.a, s, c.a), qfma(p.b, s, c.b)); }
 
+// component-wise product / fused multiply-add of two units, and a unit of two block-uniform scalars stored next to each
+// other at an 8-byte aligned address (one 64-bit load; packed operations take it as a 64-bit uniform operand)
+__device__ __forceinline__ XY<float> xy_mulv(XY<float> p, XY<float> q) { XY<float> r; r.v = __fmul2_rn(p.v, q.v); return r; }
+__device__ __forceinline__ XY<float2> xy_mulv(XY<float2> p, XY<float2> q) { return xy_make(qmul(p.a, q.a), qmul(p.b, q.b)); }
+__device__ __forceinline__ XY<float> xy_fmav(XY<float> p, XY<float> q, XY<float> c) { XY<float> r; r.v = __ffma2_rn(p.v, q.v, c.v); return r; }
+__device__ __forceinline__ XY<float2> xy_fmav(XY<float2> p, XY<float2> q, XY<float2> c) { return xy_make(qfma(p.a, q.a, c.a), qfma(p.b, q.b, c.b)); }
+template <class T> __device__ __forceinline__ XY<T> xy_uniform(const float *p);
+template <> __device__ __forceinline__ XY<float> xy_uniform<float>(const float *p) { XY<float> r; r.v = *reinterpret_cast<const float2 *>(p); return r; }
+template <> __device__ __forceinline__ XY<float2> xy_uniform<float2>(const float *p) { const float2 v = *reinterpret_cast<const float2 *>(p); return xy_make(bc2(v.x), bc2(v.y)); }
+
 // ---- sine / cosine -------------------------------------------------------------------------------------------
 // |x| <= pi/4 (every sane rollout): the same minimax polynomials sincosf evaluates after its range reduction, without the
 // reduction and quadrant logic (~11 instructions instead of ~35, same <= 1 ulp accuracy); larger angles (diverged

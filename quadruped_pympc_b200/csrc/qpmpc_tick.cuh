@@ -12,7 +12,7 @@ constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogra
 
 // shared-memory carve-up (float offsets); every region starts 16-byte aligned
 struct Smem {
-    float *in, *fref, *yaw, *w, *v, *red, *tile;
+    float *in, *fref, *yaw, *cref, *w, *v, *red, *tile;
     int *cmask;
     int *idx;                               // MAX_ELITE elite indices (CEM refit)
     __device__ Smem(float *base, const KParams &kp, int nt = TB) {
@@ -20,7 +20,8 @@ struct Smem {
         fref = in + kp.in_stride;
         yaw = fref + MAX_H;                 // {yaw0, sin yaw0, cos yaw0, -}: directly behind fref (rollouts rely on it)
         cmask = reinterpret_cast<int *>(yaw + 4);   // stance mask per step (bit l = leg l), directly behind yaw
-        w = yaw + 4 + MAX_H;                        // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
+        cref = yaw + 4 + MAX_H;                     // -(reference) of the cost pairs (KParams::qpair), directly behind cmask
+        w = cref + 8;                               // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
         v = w + 2 * nt;
         red = v + kp.P;
         idx = reinterpret_cast<int *>(red + 16);
@@ -31,7 +32,7 @@ struct Smem {
 // the CEM elite refit, nt / 4 + 1 for the four-lanes-per-sample kernel without CEM)
 __host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB, int tile_cols = TS) {
     const size_t tile = (size_t)P * tile_cols > (size_t)SCRATCH_FLOATS ? (size_t)P * tile_cols : (size_t)SCRATCH_FLOATS;
-    return (size_t)in_stride + 2 * MAX_H + 4 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
+    return (size_t)in_stride + 2 * MAX_H + 4 + 8 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
 }
 
 template <int NT>
@@ -101,6 +102,10 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
         const float nst = ((c[n] + c[H + n]) + c[2 * H + n]) + c[3 * H + n];
         s.fref[n] = kp.mg / nst;
         s.cmask[n] = (c[n] != 0.0f ? 1 : 0) | (c[H + n] != 0.0f ? 2 : 0) | (c[2 * H + n] != 0.0f ? 4 : 0) | (c[3 * H + n] != 0.0f ? 8 : 0);
+    }
+    if (threadIdx.x >= 32 && threadIdx.x < 40) {    // -(reference) in the pair order of the step cost (srbd_step)
+        const int qi[8] = {3, 4, 2, 5, 6, 7, 9, 10};
+        s.cref[threadIdx.x - 32] = -s.in[IN_REF + qi[threadIdx.x - 32]];
     }
     if (threadIdx.x == TB - 1) {    // block-uniform yaw0 and its sine / cosine (sincos_yaw)
         const float y0 = s.in[IN_STATE + 8];
