@@ -229,6 +229,15 @@ int qpmpc_publish_shm(qpmpc_handle *h, int robot, double *record, uint64_t *seq,
  * current_contact: R x 4.  Outputs R x 12 each (either may be NULL). */
 int qpmpc_stance_torques(qpmpc_handle *h, const float *feet_jac, const float *current_contact, float *grfs_contact,
                          float *tau);
+/* qpmpc_stance_torques for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments, same results; the kernel's staging area (64 floats per robot) is a file-scope static device array of
+ * QPMPC_NO_ALLOC_MAX_ROBOTS robots (256 KiB held by every GPU that loads the library, until exit) instead of the handle's
+ * lazily allocated buffer, and the call issues no cudaMalloc / cudaFree.  A handle with more robots is rejected with
+ * QPMPC_ERR_INVALID.  All calls on one device share the array: calls that overlap on the GPU race on it. */
+#define QPMPC_NO_ALLOC_MAX_ROBOTS 1024
+int qpmpc_stance_torques_static(qpmpc_handle *h, const float *feet_jac, const float *current_contact, float *grfs_contact,
+                                float *tau);
 /* costs (N) of the last tick of robot r, fetched lazily (the interface ignores them, I:138,158) */
 int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst);
 

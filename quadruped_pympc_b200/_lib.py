@@ -69,7 +69,7 @@ EXPORTS = [
     'qpmpc_destroy', 'qpmpc_num_parameters', 'qpmpc_num_local_samples', 'qpmpc_tick', 'qpmpc_tick_iterations', 'qpmpc_step', 'qpmpc_step_flat', 'qpmpc_step_reset',
     'qpmpc_step_state', 'qpmpc_tick_batched',
     'qpmpc_tick_batched_flat',
-    'qpmpc_pgg_contact_sequence', 'qpmpc_footholds_reference', 'qpmpc_step_set_shift', 'qpmpc_kernel_name', 'qpmpc_debug_host_times', 'qpmpc_shm_pack', 'qpmpc_publish_shm', 'qpmpc_stance_torques', 'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
+    'qpmpc_pgg_contact_sequence', 'qpmpc_footholds_reference', 'qpmpc_step_set_shift', 'qpmpc_kernel_name', 'qpmpc_debug_host_times', 'qpmpc_shm_pack', 'qpmpc_publish_shm', 'qpmpc_stance_torques', 'qpmpc_stance_torques_static', 'qpmpc_get_costs', 'qpmpc_rollout', 'qpmpc_generate_noise', 'qpmpc_generate_step_freqs',
     'qpmpc_shard_record_floats', 'qpmpc_shard_partial', 'qpmpc_shard_record_device_ptr', 'qpmpc_shard_finish',
     'qpmpc_shard_copy_record', 'qpmpc_shard_get_record', 'qpmpc_nccl_unique_id', 'qpmpc_shard_init_nccl',
     'qpmpc_shard_peer_export', 'qpmpc_shard_peer_attach', 'qpmpc_shard_peer_loopback', 'qpmpc_shard_peer_inject',
@@ -197,6 +197,7 @@ def load():
     lib.qpmpc_footholds_reference.argtypes = [H] + [_DP] * 7 + [C.c_double] * 4 + [_DP, C.c_int32, _DP]
     lib.qpmpc_pgg_contact_sequence.argtypes = [H, _DP, C.POINTER(C.c_uint8), _DP, C.c_double, _DP, _DP, _IP, C.c_int32, _FP]
     lib.qpmpc_stance_torques.argtypes = [H, _FP, _FP, _FP, _FP]
+    lib.qpmpc_stance_torques_static.argtypes = [H, _FP, _FP, _FP, _FP]
     lib.qpmpc_get_costs.argtypes = [H, C.c_int, _FP]
     lib.qpmpc_rollout.argtypes = [H, _FP, _FP, _FP, C.c_int32, _FP, _FP, _FP, _FP]
     lib.qpmpc_generate_noise.argtypes = [H, C.c_int, C.POINTER(C.c_uint32), _FP, _FP]

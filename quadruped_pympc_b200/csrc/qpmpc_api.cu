@@ -1388,6 +1388,60 @@ extern "C" int qpmpc_stance_torques(qpmpc_handle *h, const float *feet_jac, cons
     return QPMPC_OK;
 }
 
+// ---- qpmpc_stance_torques without any allocation ---------------------------------------------------------------------
+// (no counterpart in the reference: added for callers that may not call cudaMalloc
+// -- code under CUDA graph capture, tight serving loops, harnesses that forbid it.)
+// The staging area of stance_torque_kernel (the Jacobians and contact flags going in, the masked GRFs and torques coming
+// out: 64 floats per robot) lives in this file-scope device array instead of the handle's lazily cudaMalloc'ed d_epi:
+// QPMPC_NO_ALLOC_MAX_ROBOTS * 64 floats = 256 KiB that every GPU loading the library holds until the process exits.
+// In host code `g_static_epi` is only a host-side stand-in for the symbol, NOT a device address: static_epi_address()
+// resolves it with cudaGetSymbolAddress once per device (that device current) and the kernel is given that pointer.
+// Every call on a device shares the one array: it keeps the previous call's contents (the outputs are cleared before each
+// launch; the inputs are overwritten), and calls that overlap on the GPU (two streams, two host threads, two handles on
+// one device) race on it -- serialise them.
+static __device__ __align__(256) float g_static_epi[QPMPC_NO_ALLOC_MAX_ROBOTS * 64];
+constexpr int STATIC_EPI_MAX_DEVICES = 64;
+static float *g_static_epi_ptr[STATIC_EPI_MAX_DEVICES] = {};
+static std::mutex g_static_epi_mutex;
+
+static int static_epi_address(int device, float **ptr) {          // the caller has made `device` current
+    if (device < 0 || device >= STATIC_EPI_MAX_DEVICES) return fail(QPMPC_ERR_INVALID, "device %d: the static scratch is tracked for devices 0..%d", device, STATIC_EPI_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_static_epi_mutex);
+    if (!g_static_epi_ptr[device]) {
+        float *p = nullptr;
+        CK(cudaGetSymbolAddress((void **)&p, g_static_epi));
+        if (!p) return fail(QPMPC_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch on device %d", device);
+        g_static_epi_ptr[device] = p;
+    }
+    *ptr = g_static_epi_ptr[device];
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_stance_torques_static(qpmpc_handle *h, const float *feet_jac, const float *current_contact,
+                                           float *grfs_contact, float *tau) {
+    if (!h || !feet_jac || !current_contact) return fail(QPMPC_ERR_INVALID, "NULL argument");
+    if (h->R > QPMPC_NO_ALLOC_MAX_ROBOTS)
+        return fail(QPMPC_ERR_INVALID, "qpmpc_stance_torques_static: %d robots exceed the static scratch (QPMPC_NO_ALLOC_MAX_ROBOTS = %d); use qpmpc_stance_torques",
+                    h->R, QPMPC_NO_ALLOC_MAX_ROBOTS);
+    CK(cudaSetDevice(h->cfg.device));
+    float *scratch = nullptr;
+    const int rc = static_epi_address(h->cfg.device, &scratch);
+    if (rc) return rc;
+    const size_t R = h->R;
+    float *d_jac = scratch, *d_con = d_jac + R * 36, *d_grf = d_con + R * 4, *d_tau = d_grf + R * 12;    // d_epi's layout
+    CK(cudaMemcpyAsync(d_jac, feet_jac, R * 36 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_con, current_contact, R * 4 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(d_grf, 0, R * 24 * sizeof(float), h->stream));       // the last call's results do not survive
+    const int threads = 128, blocks = (int)((R * 12 + threads - 1) / threads);
+    stance_torque_kernel<<<blocks, threads, 0, h->stream>>>(h->kout, h->kp.out_stride, d_jac, d_con, d_grf, d_tau, (int)R);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (grfs_contact) CK(cudaMemcpyAsync(grfs_contact, d_grf, R * 12 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (tau) CK(cudaMemcpyAsync(tau, d_tau, R * 12 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_get_costs(qpmpc_handle *h, int robot, float *dst) {
     if (!h || !dst || robot < 0 || robot >= h->R) return fail(QPMPC_ERR_INVALID, "bad argument");
     CK(cudaSetDevice(h->cfg.device));
