@@ -506,7 +506,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     kp.inv_m = 1.0f / cfg->mass;                                                    // M:118
     kp.mg = (float)((double)cfg->mass * 9.81);                                      // S:380 (folded in double, then cast)
     kp.mu = cfg->mu; kp.fz_min = cfg->grf_min; kp.fz_max = cfg->grf_max;
-    memcpy(kp.I, cfg->inertia, sizeof(kp.I));
+    memcpy(kp.I, cfg->inertia, 9 * sizeof(float));
     inv3f(cfg->inertia, kp.Iinv);                                                   // M:56
     memcpy(kp.qd, cfg->q_diag, sizeof(kp.qd));
     kp.q_xyyaw = (cfg->q_diag[0] != 0.f || cfg->q_diag[1] != 0.f || cfg->q_diag[8] != 0.f) ? 1 : 0;

@@ -60,7 +60,7 @@ struct KParams {
     int off_out_sigma, off_out_elite, out_stride;
     int blk_rec_stride, shard_rec_stride;
     float inv_m, mg, mu, fz_min, fz_max;
-    float I[9], Iinv[9];
+    alignas(16) float I[12], Iinv[12];      // row-major 3 x 3 (+ padding: 128-bit uniform loads)
     float qd[12];
     int q_xyyaw;                            // 1: q_diag weights x, y or yaw (the reference's Q does not)
     uint32_t bm_bits[2];                    // 0x3F800000, 0x40000000: exponent patterns of box_muller16 (see there)
@@ -70,7 +70,7 @@ struct KParams {
     float freq_avail[3];
     float inv_ns, denom_fixed_inv;          // 1/ns ; 1/(H/ns)
     float dt[MAX_H];
-    float basis[MAX_H][4];                  // fixed gait, per step: cubic Hermite weights of the chunk's knots p0..p3 | linear (1-q, q, -, -)
+    alignas(16) float basis[MAX_H][4];      // fixed gait, per step: cubic Hermite weights of the chunk's knots p0..p3 | linear (1-q, q, -, -)
     float bounds[MAX_NS + 1];               // linspace(0,H,ns+1), S:187
     unsigned char sp_index[MAX_H];          // fixed gait: spline chunk index per step, S:189
     const float *in;                        // [R][in_stride]
@@ -454,17 +454,18 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
             if (cm & (1 << l)) {
                 XY<T> fxy;
                 T fz;
+                // spline (weights per knot) with the gravity compensation as the start of the z chain (S:382-385);
+                // x and y forces / 3 (S:388-402 with contact == 1)
                 if (PARAM == CUBIC) {
-                    fxy = xy_fma(kdxy[l], w3, xy_fma(kcxy[l], w2, xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0))));
-                    fz = qfma(kdz[l], w3, qfma(kcz[l], w2, qfma(kbz[l], w1, qmul(kaz[l], w0))));
+                    fxy = xy_mul(xy_fma(kdxy[l], w3, xy_fma(kcxy[l], w2, xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0)))), third);
+                    fz = qfma(kdz[l], w3, qfma(kcz[l], w2, qfma(kbz[l], w1, qfma(kaz[l], w0, qset<T>(fref)))));
                 } else if (PARAM == LINEAR) {
-                    fxy = xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0));
-                    fz = qfma(kbz[l], w1, qmul(kaz[l], w0));
+                    fxy = xy_mul(xy_fma(kbxy[l], w1, xy_mul(kaxy[l], w0)), third);
+                    fz = qfma(kbz[l], w1, qfma(kaz[l], w0, qset<T>(fref)));
                 } else {                                      // S:259-268
-                    fxy = knot.pair(l * PL + n, l * PL + n + H); fz = knot(l * PL + n + 2 * H);
+                    fxy = xy_mul(knot.pair(l * PL + n, l * PL + n + H), third);
+                    fz = qadd(knot(l * PL + n + 2 * H), fref);
                 }
-                fz = qadd(fz, fref);                          // S:382-385
-                fxy = xy_mul(fxy, third);                     // S:388-402 with contact == 1
                 T fx = fxy.x(), fy = fxy.y();
                 clamp_leg(kp, fx, fy, fz);                    // S:405-409
                 add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);

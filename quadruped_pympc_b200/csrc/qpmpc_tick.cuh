@@ -118,6 +118,17 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
 
 __device__ __forceinline__ bool lex_less(float c, int i, float oc, int oi) { return c < oc || (c == oc && i < oi); }
 
+// lexicographic (cost, index) minimum over a warp with two REDUX instructions: the cost through the order-preserving map
+// of its bits to unsigned (NaN-free, -0 folded into +0 by the caller's arithmetic: costs are sums of squares), then the
+// smallest index among the lanes that hold that cost.  Indices are >= 0.  Result valid in every lane.
+__device__ __forceinline__ void warp_argmin(float &c, int &i) {
+    const uint32_t b = __float_as_uint(c + 0.0f);
+    const uint32_t key = b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
+    const uint32_t kmin = __reduce_min_sync(0xffffffffu, key);
+    i = (int)__reduce_min_sync(0xffffffffu, key == kmin ? (uint32_t)i : 0xffffffffu);
+    c = __uint_as_float(kmin ^ ((kmin >> 31) ? 0x80000000u : 0xffffffffu));
+}
+
 // Online-softmax merge of `n` records (m, idx, s, V[P]) spaced `stride` floats apart in global memory.
 // Result: M, IDX (lexicographic min), S, and V in s.v (MPPI / CEM only).  All TB threads participate.
 template <int METHOD, int NT>
@@ -680,15 +691,47 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
         if (kp.mode == MODE_ROLLOUT) { __syncthreads(); continue; }
         if (blk == 0 && it == 0) phase_mark(kp, 3);
         // ---- 3. tile reduction folded into the block's running record ----
+        // (argmin | softmax weights, their sum and compaction offsets | compacted pairs): three block barriers; the same
+        // values in the same order as block_argmin + compact_weights, which the other kernels use (seven barriers)
+        const int lane = t & 31, wid = t >> 5;
         float cmin = cost;
         int imin = active ? gi : 0x7fffffff;
-        block_argmin<TB>(cmin, imin, s.red);
+        warp_argmin(cmin, imin);
+        if (lane == 0) { s.red[wid] = cmin; s.red[TB / 32 + wid] = __int_as_float(imin); }
+        __syncthreads();
+        cmin = s.red[0]; imin = __float_as_int(s.red[TB / 32]);
+#pragma unroll
+        for (int k = 1; k < TB / 32; ++k) {
+            const float oc = s.red[k];
+            const int oi = __float_as_int(s.red[TB / 32 + k]);
+            if (lex_less(oc, oi, cmin, imin)) { cmin = oc; imin = oi; }
+        }
         if (METHOD != RANDOM_SAMPLING) {
             const float m_new = fminf(m_run, cmin);              // cmin is finite: the tile has >= 1 active sample
             const float scale_old = (m_run == CUDART_INF_F) ? 0.0f : expf(-(m_run - m_new));
             const float w = active ? expf(-(cost - m_new)) : 0.0f;   // exp(-(c - beta)/T), T = 1, S:828-830
-            float s_tile;
-            const int nnz = compact_weights<TB>(w, t, true, s, s_tile);
+            // only the non-zero weights are published, as (weight, sample slot) pairs in ascending slot order
+            // (compact_weights); their sum in block_sum's fixed order
+            const bool nzb = w != 0.0f;
+            const unsigned int nz = __ballot_sync(0xffffffffu, nzb);
+            float wsum = w;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+            float *s_sum = s.red + 2 * (TB / 32);
+            int *s_cnt = reinterpret_cast<int *>(s.red + 3 * (TB / 32));
+            if (lane == 0) { s_sum[wid] = wsum; s_cnt[wid] = __popc(nz); }
+            __syncthreads();
+            float s_tile = s_sum[0];
+            int off = __popc(nz & ((1u << lane) - 1u)), nnz = 0;
+#pragma unroll
+            for (int k = 0; k < TB / 32; ++k) {
+                const int c = s_cnt[k];
+                if (k > 0) s_tile += s_sum[k];
+                nnz += c;
+                if (k < wid) off += c;
+            }
+            if (nzb) reinterpret_cast<float2 *>(s.w)[off] = make_float2(w, __int_as_float(t));
+            __syncthreads();
             s_run = fmaf(s_run, scale_old, s_tile);
             const float2 *wi = reinterpret_cast<const float2 *>(s.w);
             for (int p = t; p < kp.P; p += TB) {
