@@ -284,6 +284,13 @@ __device__ __forceinline__ float sample_step_freq(const KParams &kp, const float
 // Written once for T = float (one sample per thread) and T = float2 (two samples per thread, packed FP32):
 // see qpmpc_math.cuh -- explicit round-to-nearest operations only, so both lane types give the same bits.
 // ======================================================================================================
+// 0, but not to the compiler (see rollout_fixed_t)
+__device__ __forceinline__ int opaque_zero() {
+    int z;
+    asm volatile("mov.u32 %0, 0;" : "=r"(z));
+    return z;
+}
+
 template <class T> struct BodyT { T px, py, pz, vx, vy, vz, roll, pitch, yaw, wx, wy, wz; };
 typedef BodyT<float> Body;
 
@@ -408,10 +415,16 @@ struct Knots1 {                       // one sample per thread: tile column `tco
 // S:388-402 and M:111-116).  s_fref[n] = mass*9.81 / n_stance(n) (S:377-380).
 template <int PARAM, class T, class KNOTS>
 __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_in, const float *s_fref, const KNOTS &knot) {
-    const float *s_yaw = s_fref + MAX_H;
     const int *s_cmask = reinterpret_cast<const int *>(s_fref + MAX_H + 4);   // stance mask per step (stage_inputs)
-    const float *ref = s_in + IN_REF;
-    const float *feet = s_in + IN_STATE + 12;
+    // The block-uniform operands of the step (feet, reference, yaw0) are read through a pointer the compiler cannot prove
+    // uniform (+ an opaque zero): one base register and LDS [R + imm].  As uniform addresses every group of loads
+    // re-derives the CTA's shared-memory window (S2UR + UMOV + ULEA, ~8 issue slots per step: the uniform registers are
+    // taken by the constants of the step).  The stance masks stay uniform: their branches must not look divergent.
+    const int zero = opaque_zero();
+    const float *s_inv = s_in + zero, *s_frefv = s_fref + zero;
+    const float *s_yaw = s_frefv + MAX_H;
+    const float *ref = s_inv + IN_REF;
+    const float *feet = s_inv + IN_STATE + 12;
     BodyT<T> b = load_body_t<T>(s_in + IN_STATE);
     T cost = qset<T>(0.0f);
     const int H = kp.H, PL = kp.P_leg;

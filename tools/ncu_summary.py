@@ -1,6 +1,6 @@
 """Summarise an `ncu --set full` capture (.ncu-rep) into the small tracked files under profiles/.
 
-    python tools/ncu_summary.py gpurun_out/prof_X.ncu-rep profiles/X [--top 40]
+    python tools/ncu_summary.py gpurun_out/prof_X.ncu-rep profiles/X [--top 40] [--all-sass]
 
 Writes  <out>_summary.json   per-launch key metrics (duration, DRAM bytes, instruction mix, issue / FMA-pipe
                              utilisation, occupancy limits, warp stall breakdown)
@@ -111,6 +111,13 @@ def main():
                 for r in lst:
                     st = max(stall_cols, key=lambda i: num(r[i]))
                     w.writerow([tag, r[ci], r[csmp], h[st] if num(r[st]) > 0 else '', r[cs].strip()])
+        if '--all-sass' in sys.argv:           # every instruction in address order (regions of a kernel: see tools/sass_regions.py)
+            with open(out + '_all_sass.csv', 'w', newline='') as f:
+                w = csv.writer(f)
+                w.writerow(['address', 'inst_executed', 'stall_samples', 'top_stall', 'sass'])
+                for r in body:
+                    st = max(stall_cols, key=lambda i: num(r[i]))
+                    w.writerow([r[0], r[ci], r[csmp], h[st] if num(r[st]) > 0 else '', r[cs].strip()])
         # opcode histogram (executed warp instructions per SASS mnemonic)
         ops = {}
         for r in body:
