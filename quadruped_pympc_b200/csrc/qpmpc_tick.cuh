@@ -635,6 +635,7 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
     float *tcol = s.tile + t;
     float m_run = CUDART_INF_F, s_run = 0.0f;
     int idx_run = 0x7fffffff;
+    int grp = blk * (kp.iters / kp.iters_rec), grp_tiles = 0;     // record group of the current tile, tiles folded into it
     if (hlp == 0)
         for (int p = t; p < kp.P; p += TB) s.v[p] = 0.0f;
 
@@ -658,7 +659,7 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
                 const NoiseRow nr = noise_row<METHOD>(kp, gi);
                 const int nq = kp.P >> 2, noct = (nq + 1) >> 1;      // one Philox block per oct (8 knots)
                 float *tp = tcol + hlp * 8 * TS;
-#pragma unroll 2
+#pragma unroll 4
                 for (int c = hlp; c < noct; c += NH, tp += NH * 8 * TS) {
                     float4 lo, hi;
                     noise_oct_nz<METHOD>(nr, seed, robot, tick, c, s_sigma, lo, hi);
@@ -748,9 +749,10 @@ __device__ __forceinline__ void tick_body(const KParams &kp, int &s_last) {
         if (lex_less(cmin, imin, m_run, idx_run)) { m_run = cmin; idx_run = imin; }   // running (min, argmin), S:690
         // one record per group of kp.iters_rec tiles (or at the shard's last tile): a block that walks several groups
         // (batched launches amortise their staging that way) leaves exactly the records one-group blocks would
-        const int T = blk * kp.iters + it;
-        if ((T + 1) % kp.iters_rec == 0 || (T + 1) * TB >= kp.n_local) {
-            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + T / kp.iters_rec) * kp.blk_rec_stride;
+        // (kp.iters is a multiple of kp.iters_rec, so a block's first tile opens a group: counters, no division)
+        if (++grp_tiles == kp.iters_rec || tile_base + TB >= kp.n_local) {
+            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + grp) * kp.blk_rec_stride;
+            ++grp; grp_tiles = 0;
             if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
             if (METHOD != RANDOM_SAMPLING)
                 for (int p = t; p < kp.P; p += TB) { rec[REC_V + p] = s.v[p]; s.v[p] = 0.0f; }
