@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
     int idx_run = 0x7fffffff;
     for (int p = t; p < kp.P; p += XTB) s.v[p] = 0.0f;
 
+    int grp = blk * (kp.iters / kp.iters_rec), grp_tiles = 0;     // record group of the current tile, tiles folded into it
     for (int it = 0; it < kp.iters; ++it) {
         const int tile_base = (blk * kp.iters + it) * XS;       // local (shard) index of this tile's first sample
         if (tile_base >= kp.n_local) break;                     // block-uniform
@@ -155,9 +156,10 @@ __global__ void __launch_bounds__(XTB, 2) tick_kernel_x2(const __grid_constant__
         if (lex_less(cmin, imin, m_run, idx_run)) { m_run = cmin; idx_run = imin; }   // running (min, argmin), S:690
         // one record per group of kp.iters_rec tiles (or at the shard's last tile): a block that walks several groups
         // (batched launches amortise their staging that way) leaves exactly the records one-group blocks would
-        const int T = blk * kp.iters + it;
-        if ((T + 1) % kp.iters_rec == 0 || (T + 1) * XS >= kp.n_local) {
-            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + T / kp.iters_rec) * kp.blk_rec_stride;
+        // (kp.iters is a multiple of kp.iters_rec, so a block's first tile opens a group: counters, no division)
+        if (++grp_tiles == kp.iters_rec || (blk * kp.iters + it + 1) * XS >= kp.n_local) {
+            float *rec = kp.blk_recs + ((size_t)r * kp.nrec + grp) * kp.blk_rec_stride;
+            ++grp; grp_tiles = 0;
             if (t == 0) { rec[REC_M] = m_run; rec[REC_IDX] = __int_as_float(idx_run); rec[REC_S] = s_run; rec[REC_PAD] = 0.0f; }
             if (METHOD != RANDOM_SAMPLING)
                 for (int p = t; p < kp.P; p += XTB) { rec[REC_V + p] = s.v[p]; s.v[p] = 0.0f; }
