@@ -64,7 +64,7 @@ struct KParams {
     float qd[12];
     int q_xyyaw;                            // 1: q_diag weights x, y or yaw (the reference's Q does not)
     uint32_t bm_bits[2];                    // 0x3F800000, 0x40000000: exponent patterns of box_muller16 (see there)
-    alignas(8) float qpair[8];              // q_diag as the pairs srbd_step sums: (vx,vy) (z,vz) (roll,pitch) (wx,wy)
+    alignas(16) float qpair[8];              // q_diag as the pairs srbd_step sums: (vx,vy) (z,vz) (roll,pitch) (wx,wy)
     float mpc_dt, duty;
     float sigma_rs[3], sigma_mppi;
     float freq_avail[3];
@@ -307,13 +307,18 @@ __device__ __forceinline__ void clamp_leg(const KParams &kp, T &fx, T &fy, T &fz
 
 // Fx..: sum of stance forces; tx..: sum of (foot - com) x F (world frame), M:111-118,132-135
 template <class T>
-__device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, const float *foot, T fx, T fy, T fz,
+__device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, float footx, float footy, float footz, T fx, T fy, T fz,
                                         T &Fx, T &Fy, T &Fz, T &tx, T &ty, T &tz) {
-    const T rx = qsub(foot[0], b.px), ry = qsub(foot[1], b.py), rz = qsub(foot[2], b.pz);
+    const T rx = qsub(footx, b.px), ry = qsub(footy, b.py), rz = qsub(footz, b.pz);
     Fx = qadd(Fx, fx); Fy = qadd(Fy, fy); Fz = qadd(Fz, fz);
     tx = qfnma(rz, fy, qfma(ry, fz, tx));               // the moment accumulates term by term: two FMAs per component
     ty = qfnma(rx, fz, qfma(rz, fx, ty));
     tz = qfnma(ry, fx, qfma(rx, fy, tz));
+}
+template <class T>
+__device__ __forceinline__ void add_leg(const KParams &kp, const BodyT<T> &b, const float *foot, T fx, T fy, T fz,
+                                        T &Fx, T &Fy, T &Fz, T &tx, T &ty, T &tz) {
+    add_leg(kp, b, foot[0], foot[1], foot[2], fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
 }
 
 // one term of e^T Q e on the state after the step, S:450-451 (the reference's Q also weights x, y, yaw with 0: kept, so
@@ -326,9 +331,9 @@ __device__ __forceinline__ void cost_term(T &c, T x, float ref, float q) {
 
 // two terms of e^T Q e as one unit: nref = -(reference pair) (shared memory, stage_inputs), q = weight pair (KParams::qpair)
 template <class T>
-__device__ __forceinline__ void cost_pair(XY<T> &acc, T x, T y, const float *nref, const float *q) {
-    const XY<T> e = xy_add(xy_make(x, y), xy_uniform<T>(nref));
-    acc = xy_fmav(xy_mulv(e, xy_uniform<T>(q)), e, acc);
+__device__ __forceinline__ void cost_pair(XY<T> &acc, T x, T y, XY<T> nref, XY<T> q) {
+    const XY<T> e = xy_add(xy_make(x, y), nref);
+    acc = xy_fmav(xy_mulv(e, q), e, acc);
 }
 
 template <class T>
@@ -372,9 +377,9 @@ __device__ __forceinline__ T srbd_step(const KParams &kp, BodyT<T> &b, T Fx, T F
     XY<T> acc;
     { const XY<T> e = xy_add(xy_make(b.vx, b.vy), xy_uniform<T>(nref));
       acc = xy_mulv(xy_mulv(e, xy_uniform<T>(kp.qpair)), e); }
-    cost_pair(acc, b.pz, b.vz, nref + 2, kp.qpair + 2);
-    cost_pair(acc, b.roll, b.pitch, nref + 4, kp.qpair + 4);
-    cost_pair(acc, b.wx, b.wy, nref + 6, kp.qpair + 6);
+    cost_pair(acc, b.pz, b.vz, xy_uniform<T>(nref + 2), xy_uniform<T>(kp.qpair + 2));
+    cost_pair(acc, b.roll, b.pitch, xy_uniform<T>(nref + 4), xy_uniform<T>(kp.qpair + 4));
+    cost_pair(acc, b.wx, b.wy, xy_uniform<T>(nref + 6), xy_uniform<T>(kp.qpair + 6));
     T c = qadd(acc.x(), acc.y());
     cost_term(c, b.wz, ref[11], kp.qd[11]);
     // the reference's Q weights x, y and yaw with 0 (S:118-130): (e * 0) * e adds exactly nothing for every finite e, so
@@ -424,7 +429,7 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
     const float *s_inv = s_in + zero, *s_frefv = s_fref + zero;
     const float *s_yaw = s_frefv + MAX_H;
     const float *ref = s_inv + IN_REF;
-    const float *feet = s_inv + IN_STATE + 12;
+    const float4 *feet4 = reinterpret_cast<const float4 *>(s_frefv + 2 * MAX_H + 4 + 8);     // Smem::feet4
     BodyT<T> b = load_body_t<T>(s_in + IN_STATE);
     T cost = qset<T>(0.0f);
     const int H = kp.H, PL = kp.P_leg;
@@ -481,7 +486,8 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
                 }
                 T fx = fxy.x(), fy = fxy.y();
                 clamp_leg(kp, fx, fy, fz);                    // S:405-409
-                add_leg(kp, b, feet + 3 * l, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
+                const float4 ft = feet4[l];
+                add_leg(kp, b, ft.x, ft.y, ft.z, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }
         }
         cost = qadd(cost, srbd_step(kp, b, Fx, Fy, Fz, tx, ty, tz, kp.dt[n], ref, s_yaw));   // S:446-451,491

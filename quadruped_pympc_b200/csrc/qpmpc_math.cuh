@@ -90,6 +90,9 @@ __device__ __forceinline__ XY<float> xy_mulv(XY<float> p, XY<float> q) { XY<floa
 __device__ __forceinline__ XY<float2> xy_mulv(XY<float2> p, XY<float2> q) { return xy_make(qmul(p.a, q.a), qmul(p.b, q.b)); }
 __device__ __forceinline__ XY<float> xy_fmav(XY<float> p, XY<float> q, XY<float> c) { XY<float> r; r.v = __ffma2_rn(p.v, q.v, c.v); return r; }
 __device__ __forceinline__ XY<float2> xy_fmav(XY<float2> p, XY<float2> q, XY<float2> c) { return xy_make(qfma(p.a, q.a, c.a), qfma(p.b, q.b, c.b)); }
+template <class T> __device__ __forceinline__ XY<T> xy_uniform2(float x, float y);
+template <> __device__ __forceinline__ XY<float> xy_uniform2<float>(float x, float y) { return xy_make(x, y); }
+template <> __device__ __forceinline__ XY<float2> xy_uniform2<float2>(float x, float y) { return xy_make(bc2(x), bc2(y)); }
 template <class T> __device__ __forceinline__ XY<T> xy_uniform(const float *p);
 template <> __device__ __forceinline__ XY<float> xy_uniform<float>(const float *p) { XY<float> r; r.v = *reinterpret_cast<const float2 *>(p); return r; }
 template <> __device__ __forceinline__ XY<float2> xy_uniform<float2>(const float *p) { const float2 v = *reinterpret_cast<const float2 *>(p); return xy_make(bc2(v.x), bc2(v.y)); }

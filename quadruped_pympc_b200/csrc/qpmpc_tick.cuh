@@ -12,7 +12,7 @@ constexpr int SCRATCH_FLOATS = 2 * SCRATCH_KEYS + 256 + 16;   // keys + histogra
 
 // shared-memory carve-up (float offsets); every region starts 16-byte aligned
 struct Smem {
-    float *in, *fref, *yaw, *cref, *w, *v, *red, *tile;
+    float *in, *fref, *yaw, *cref, *feet4, *w, *v, *red, *tile;
     int *cmask;
     int *idx;                               // MAX_ELITE elite indices (CEM refit)
     __device__ Smem(float *base, const KParams &kp, int nt = TB) {
@@ -21,7 +21,8 @@ struct Smem {
         yaw = fref + MAX_H;                 // {yaw0, sin yaw0, cos yaw0, -}: directly behind fref (rollouts rely on it)
         cmask = reinterpret_cast<int *>(yaw + 4);   // stance mask per step (bit l = leg l), directly behind yaw
         cref = yaw + 4 + MAX_H;                     // -(reference) of the cost pairs (KParams::qpair), directly behind cmask
-        w = cref + 8;                               // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
+        feet4 = cref + 8;                           // the four feet as (x, y, z, 0): one 128-bit load per stance leg and step
+        w = feet4 + 16;                             // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
         v = w + 2 * nt;
         red = v + kp.P;
         idx = reinterpret_cast<int *>(red + 16);
@@ -32,7 +33,7 @@ struct Smem {
 // the CEM elite refit, nt / 4 + 1 for the four-lanes-per-sample kernel without CEM)
 __host__ __device__ inline size_t smem_floats(int in_stride, int P, int nt = TB, int tile_cols = TS) {
     const size_t tile = (size_t)P * tile_cols > (size_t)SCRATCH_FLOATS ? (size_t)P * tile_cols : (size_t)SCRATCH_FLOATS;
-    return (size_t)in_stride + 2 * MAX_H + 4 + 8 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
+    return (size_t)in_stride + 2 * MAX_H + 4 + 8 + 16 + 2 * nt + P + 16 + MAX_ELITE + tile + 4;
 }
 
 template <int NT>
@@ -106,6 +107,10 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
     if (threadIdx.x >= 32 && threadIdx.x < 40) {    // -(reference) in the pair order of the step cost (srbd_step)
         const int qi[8] = {3, 4, 2, 5, 6, 7, 9, 10};
         s.cref[threadIdx.x - 32] = -s.in[IN_REF + qi[threadIdx.x - 32]];
+    }
+    if (threadIdx.x >= 64 && threadIdx.x < 80) {    // feet padded to four floats each (rollout_fixed_t)
+        const int i = threadIdx.x - 64;
+        s.feet4[i] = (i & 3) == 3 ? 0.0f : s.in[IN_STATE + 12 + 3 * (i >> 2) + (i & 3)];
     }
     if (threadIdx.x == TB - 1) {    // block-uniform yaw0 and its sine / cosine (sincos_yaw)
         const float y0 = s.in[IN_STATE + 8];
