@@ -59,7 +59,7 @@ struct KParams {
     int off_best, off_sigma, in_stride;
     int off_out_sigma, off_out_elite, out_stride;
     int blk_rec_stride, shard_rec_stride;
-    float inv_m, mg, mu, fz_min, fz_max;
+    float inv_m, mg, fz_min, fz_max, mu;    // (fz_min, fz_max): an aligned pair, one 64-bit uniform load per clamped leg
     alignas(16) float I[12], Iinv[12];      // row-major 3 x 3 (+ padding: 128-bit uniform loads)
     float qd[12];
     int q_xyyaw;                            // 1: q_diag weights x, y or yaw (the reference's Q does not)
@@ -298,12 +298,14 @@ typedef BodyT<float> Body;
 // == fminf(x, hi) for every input the reference can produce, NaN included (a NaN force takes the bound, as `where`
 // does; only the sign of a zero can differ, which no later product can see): one FMNMX instead of FSETP + FSEL.
 template <class T>
-__device__ __forceinline__ void clamp_leg(const KParams &kp, T &fx, T &fy, T &fz) {
+__device__ __forceinline__ void clamp_leg(const KParams &kp, float mu, T &fx, T &fy, T &fz) {
     fz = qmin(qmax(fz, kp.fz_min), kp.fz_max);
-    const T hi = qmul(fz, kp.mu), lo = qneg(hi);
+    const T hi = qmul(fz, mu), lo = qneg(hi);
     fx = qmin(qmax(fx, lo), hi);
     fy = qmin(qmax(fy, lo), hi);
 }
+template <class T>
+__device__ __forceinline__ void clamp_leg(const KParams &kp, T &fx, T &fy, T &fz) { clamp_leg(kp, kp.mu, fx, fy, fz); }
 
 // Fx..: sum of stance forces; tx..: sum of (foot - com) x F (world frame), M:111-118,132-135
 template <class T>
@@ -485,8 +487,8 @@ __device__ __forceinline__ T rollout_fixed_t(const KParams &kp, const float *s_i
                     fz = qadd(knot(l * PL + n + 2 * H), fref);
                 }
                 T fx = fxy.x(), fy = fxy.y();
-                clamp_leg(kp, fx, fy, fz);                    // S:405-409
-                const float4 ft = feet4[l];
+                const float4 ft = feet4[l];                   // (foot x, y, z, mu)
+                clamp_leg(kp, ft.w, fx, fy, fz);              // S:405-409
                 add_leg(kp, b, ft.x, ft.y, ft.z, fx, fy, fz, Fx, Fy, Fz, tx, ty, tz);
             }
         }

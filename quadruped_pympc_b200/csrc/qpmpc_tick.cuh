@@ -21,7 +21,7 @@ struct Smem {
         yaw = fref + MAX_H;                 // {yaw0, sin yaw0, cos yaw0, -}: directly behind fref (rollouts rely on it)
         cmask = reinterpret_cast<int *>(yaw + 4);   // stance mask per step (bit l = leg l), directly behind yaw
         cref = yaw + 4 + MAX_H;                     // -(reference) of the cost pairs (KParams::qpair), directly behind cmask
-        feet4 = cref + 8;                           // the four feet as (x, y, z, 0): one 128-bit load per stance leg and step
+        feet4 = cref + 8;                           // the four feet as (x, y, z, mu): one 128-bit load per stance leg and step
         w = feet4 + 16;                             // 2 * nt floats: compacted (weight, sample slot) pairs of one tile
         v = w + 2 * nt;
         red = v + kp.P;
@@ -108,9 +108,9 @@ __device__ __forceinline__ void stage_inputs(const KParams &kp, int r, const Sme
         const int qi[8] = {3, 4, 2, 5, 6, 7, 9, 10};
         s.cref[threadIdx.x - 32] = -s.in[IN_REF + qi[threadIdx.x - 32]];
     }
-    if (threadIdx.x >= 64 && threadIdx.x < 80) {    // feet padded to four floats each (rollout_fixed_t)
+    if (threadIdx.x >= 64 && threadIdx.x < 80) {    // feet padded to four floats each, the friction coefficient in the fourth (rollout_fixed_t)
         const int i = threadIdx.x - 64;
-        s.feet4[i] = (i & 3) == 3 ? 0.0f : s.in[IN_STATE + 12 + 3 * (i >> 2) + (i & 3)];
+        s.feet4[i] = (i & 3) == 3 ? kp.mu : s.in[IN_STATE + 12 + 3 * (i >> 2) + (i & 3)];
     }
     if (threadIdx.x == TB - 1) {    // block-uniform yaw0 and its sine / cosine (sincos_yaw)
         const float y0 = s.in[IN_STATE + 8];
