@@ -542,6 +542,35 @@ __device__ __forceinline__ void spline_dyn(const KParams &kp, const float *s_bes
     fx = f[0]; fy = f[1]; fz = f[2];
 }
 
+// The same cubic spline with the chunk's knots kept in registers: a leg's chunk index changes at most ns - 1 times over the
+// horizon, so p1, phi, p2, phi_next of the three axes (the same sums as spline_dyn) are rebuilt only when it does --
+// 24 shared loads and 27 additions per stance leg and step less, identical results.
+struct ChunkKnots { float v[12]; int idx; };   // per leg: [axis][p1, phi, p2, phi_next]
+__device__ __forceinline__ void spline_dyn_cubic_cached(const KParams &kp, const float *s_best, const float *tcol, int l, int step,
+                                                        float inv_denom, ChunkKnots &ck, float &fx, float &fy, float &fz) {
+    const float stepf = (float)step;
+    int idx = 0;
+    for (int i = 1; i <= kp.ns; ++i) idx = (stepf >= kp.bounds[i]) ? i : idx;      // S:187-189
+    idx = idx < kp.ns ? idx : kp.ns - 1;
+    const float q = fmaf(stepf, inv_denom, -(float)idx);                           // S:191-194
+    if (idx != ck.idx) {
+        ck.idx = idx;
+        const int s0 = 10 * idx;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            const float p0 = QP_KNOT(l, s0 + 4 * ax), p1 = QP_KNOT(l, s0 + 4 * ax + 1), p2 = QP_KNOT(l, s0 + 4 * ax + 2),
+                        p3 = QP_KNOT(l, s0 + 4 * ax + 3);
+            ck.v[4 * ax] = p1; ck.v[4 * ax + 1] = 0.5f * ((p2 - p1) + (p1 - p0));
+            ck.v[4 * ax + 2] = p2; ck.v[4 * ax + 3] = 0.5f * ((p3 - p2) + (p2 - p1));
+        }
+    }
+    const float q2 = q * q, q3 = q2 * q;
+    const float a = 2.0f * q3 - 3.0f * q2 + 1.0f, bb = q3 - 2.0f * q2 + q, c = -2.0f * q3 + 3.0f * q2, d = q3 - q2;
+    fx = a * ck.v[0] + bb * ck.v[1] + c * ck.v[2] + d * ck.v[3];
+    fy = a * ck.v[4] + bb * ck.v[5] + c * ck.v[6] + d * ck.v[7];
+    fz = a * ck.v[8] + bb * ck.v[9] + c * ck.v[10] + d * ck.v[11];
+}
+
 // Gait-adaptive rollout (A:326-501): per-sample contact sequence from the phase clock (G:68-89,136-151),
 // per-leg stance counters as spline clocks, plus the step-frequency cost A:500.
 template <int PARAM>
@@ -570,6 +599,9 @@ __device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float
     }
     Body b = load_body(s_in + IN_STATE);
     float cost = 0.0f;
+    ChunkKnots ck[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) ck[l].idx = -1;
 #pragma unroll 1
     for (int n = 0; n < H; ++n) {
         float c[4];
@@ -590,7 +622,8 @@ __device__ __forceinline__ float rollout_adaptive(const KParams &kp, const float
         for (int l = 0; l < 4; ++l) {
             if (c[l] != 0.0f) {                                // swing legs contribute exactly zero (see rollout_fixed)
                 float fx, fy, fz;
-                spline_dyn<PARAM>(kp, s_best, tcol, l, nleg[l], inv_denom[l], fx, fy, fz);
+                if (PARAM == CUBIC) spline_dyn_cubic_cached(kp, s_best, tcol, l, nleg[l], inv_denom[l], ck[l], fx, fy, fz);
+                else spline_dyn<PARAM>(kp, s_best, tcol, l, nleg[l], inv_denom[l], fx, fy, fz);
                 fz = fref + fz;
                 fx = fx * third; fy = fy * third;
                 clamp_leg(kp, fx, fy, fz);
